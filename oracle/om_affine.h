@@ -110,6 +110,22 @@ inline std::vector<AffineSol> solve_scale_and_shift_shared_focal(const double x1
         double den = -poly_eval(ab, b1);
         if (den == 0) continue;
         double w = poly_eval(ac, b1) / den;
+        // Newton polish of (b1, w) on the two quadratics-in-w (the expanded
+        // degree-8 resultant is only a root *locator*; its coefficients lose digits)
+        for (int it = 0; it < 6; it++) {
+            double da, db, dc, da2, db2, dc2;
+            double va = poly_eval_d(a, b1, &da), vb = poly_eval_d(b, b1, &db), vc = poly_eval_d(c, b1, &dc);
+            double va2 = poly_eval_d(a2, b1, &da2), vb2 = poly_eval_d(b2, b1, &db2), vc2 = poly_eval_d(c2, b1, &dc2);
+            double F1 = (va * w + vb) * w + vc, F2 = (va2 * w + vb2) * w + vc2;
+            double J11 = (da * w + db) * w + dc, J12 = 2 * va * w + vb;
+            double J21 = (da2 * w + db2) * w + dc2, J22 = 2 * va2 * w + vb2;
+            double det = J11 * J22 - J12 * J21;
+            if (det == 0 || !std::isfinite(det)) break;
+            double s1 = (F1 * J22 - F2 * J12) / det, s2 = (J11 * F2 - J21 * F1) / det;
+            if (!std::isfinite(s1) || !std::isfinite(s2)) break;
+            b1 -= s1; w -= s2;
+            if (std::fabs(s1) <= 1e-16 * std::fabs(b1) && std::fabs(s2) <= 1e-16 * std::fabs(w)) break;
+        }
         double y1 = w * poly_eval(g[1], b1) + h[1], y2 = w * poly_eval(g[2], b1) + h[2];
         double s = w * poly_eval(g[3], b1) + h[3];
         if (w < 0 || !(s > 0) || !std::isfinite(w) || !std::isfinite(s)) continue;

@@ -78,7 +78,36 @@ struct SturmChain {
 };
 
 // all distinct real roots, ascending
+inline std::vector<double> poly_real_roots_unscaled(std::vector<double> p);
 inline std::vector<double> poly_real_roots(std::vector<double> p) {
+    // balance coefficients with x = s*y, s = |p0/pn|^(1/n) (roots of size ~1)
+    while (p.size() > 1 && p.back() == 0.0) p.pop_back();
+    int n = (int)p.size() - 1;
+    if (n >= 2 && p[0] != 0.0 && std::isfinite(p[0]) && std::isfinite(p[n])) {
+        double s = std::pow(std::fabs(p[0] / p[n]), 1.0 / n);
+        if (s > 0 && std::isfinite(s)) {
+            std::vector<double> q(p);
+            double sp = 1.0;
+            for (int i = 0; i <= n; i++) { q[i] = p[i] * sp; sp *= s; }
+            double qn = q[n];
+            for (double &c : q) c /= qn;
+            std::vector<double> r = poly_real_roots_unscaled(q);
+            for (double &x : r) {
+                x *= s;
+                for (int it = 0; it < 4; it++) { // polish on the original coefficients
+                    double d, f = poly_eval_d(p, x, &d);
+                    if (d == 0 || !std::isfinite(f / d)) break;
+                    double xn = x - f / d;
+                    if (xn == x) break;
+                    x = xn;
+                }
+            }
+            return r;
+        }
+    }
+    return poly_real_roots_unscaled(p);
+}
+inline std::vector<double> poly_real_roots_unscaled(std::vector<double> p) {
     std::vector<double> roots;
     poly_trim(p);
     int n = (int)p.size() - 1;
