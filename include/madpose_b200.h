@@ -1,0 +1,144 @@
+/* madpose_b200 C ABI -- the drop-in boundary of the B200-native hybrid LO-RANSAC path.
+ *
+ * The reference (kocurvik/madpose) has no C ABI: its only plugin interface is the
+ * pybind11 module built from src/bindings.cpp.  This header is what our own
+ * bindings.cpp (madpose_b200/csrc/bindings.cpp, same Python names and fields as
+ * /root/reference/src/bindings.cpp:78-174) binds.  Plain pointers and sizes, no
+ * torch / Eigen / STL types, caller-owned buffers, int status returns
+ * (0 = ok, negative = error, text via mp_last_error()).  Every entry point runs
+ * on the GPU; there is no CPU fallback (MP_ERR_NO_DEVICE if no sm_100 device).
+ */
+#ifndef MADPOSE_B200_H_
+#define MADPOSE_B200_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { MP_OK = 0, MP_ERR_ARG = -1, MP_ERR_NO_DEVICE = -2, MP_ERR_CUDA = -3, MP_ERR_ALLOC = -4 };
+
+/* estimator kind: which of the three Python entry points the call serves
+ * (bindings.cpp:169-174) */
+enum { MP_KIND_CALIBRATED = 0, MP_KIND_SHARED_FOCAL = 1, MP_KIND_TWO_FOCAL = 2 };
+
+/* madpose.HybridLORansacOptions: ExtendedHybridLORansacOptions
+ * (src/hybrid_ransac.h:17-25) over ransac_lib::HybridLORansacOptions
+ * (ext/RansacLib/RansacLib/hybrid_ransac.h:47-93); defaults are those. */
+typedef struct mp_options {
+    uint32_t min_num_iterations;            /* 100   */
+    uint32_t max_num_iterations;            /* 10000 */
+    uint32_t max_num_iterations_per_solver; /* 10000 */
+    uint32_t random_seed;                   /* 0     */
+    double success_probability;             /* 0.9999 */
+    double squared_inlier_thresholds[2];    /* [reprojection px^2, sampson px^2]; caller must set */
+    double data_type_weights[2];            /* caller must set */
+    double threshold_multiplier;            /* sqrt(2) */
+    int32_t num_lo_steps;                   /* 10 */
+    int32_t num_lsq_iterations;             /* 4  */
+    int32_t min_sample_multiplicator;       /* 7  */
+    int32_t non_min_sample_multiplier;      /* 3  */
+    uint32_t lo_starting_iterations;        /* 50 */
+    int32_t final_least_squares;            /* 0  */
+    int32_t use_ours;                       /* 0 (alternative solvers: not implemented, must be 0) */
+    int32_t use_4p4d;                       /* 0 (must be 0) */
+} mp_options;
+
+/* madpose.EstimatorConfig (src/estimator_config.h:5-33) */
+typedef struct mp_config {
+    int32_t solver_type; /* 0 HYBRID, 1 EPI_ONLY, 2 MD_ONLY */
+    int32_t score_type;
+    int32_t lo_type;
+    int32_t min_depth_constraint; /* 1 */
+    int32_t use_shift;            /* 1 */
+    int32_t ceres_use_nonmonotonic_steps; /* 1 */
+    int32_t ceres_num_threads;    /* ignored: the LM runs on the device */
+    int32_t reserved_;
+    double ceres_function_tolerance;  /* 1e-6 */
+    double ceres_gradient_tolerance;  /* 1e-8 */
+    double ceres_parameter_tolerance; /* 1e-6 */
+    double ceres_max_num_iterations;  /* 25 */
+} mp_config;
+
+/* One image pair as the Python call receives it (bindings.cpp:169-174):
+ * x0,x1 = n x 2 row-major pixel coordinates, d0,d1 = n prior depths.
+ * Calibrated uses K0,K1 (row-major 3x3); the focal kinds use pp0,pp1. */
+typedef struct mp_pair {
+    int32_t n;
+    int32_t reserved_;
+    const double *x0, *x1, *d0, *d1; /* HOST pointers */
+    double min_depth[2];
+    double K0[9], K1[9];
+    double pp0[2], pp1[2];
+} mp_pair;
+
+/* A model = PoseScaleOffset / ...SharedFocal / ...TwoFocal (src/pose.h:7-56):
+ * R row-major (9), t (3), scale, offset0, offset1, focal0, focal1
+ * (calibrated: focals = 1; shared focal: focal0 == focal1 == focal). */
+#define MP_MODEL_DOUBLES 17
+typedef struct mp_model { double R[9], t[3], scale, offset0, offset1, focal0, focal1; } mp_model;
+
+/* ransac_lib::HybridRansacStatistics (ext/RansacLib/RansacLib/hybrid_ransac.h:95-104).
+ * inlier_indices[t] are returned through the caller's `inliers` buffer. */
+typedef struct mp_stats {
+    uint32_t num_iterations_total;
+    uint32_t num_iterations_per_solver[2];
+    int32_t best_num_inliers;
+    int32_t best_solver_type;
+    int32_t number_lo_iterations;
+    int32_t num_inliers[3]; /* lengths of the three inlier lists */
+    int32_t reserved_;
+    double best_model_score;
+    double inlier_ratios[3];
+    /* extra counters (not part of the reference struct) */
+    uint64_t hypotheses_scored; /* models passed through scoring (minimal + LO) */
+    uint64_t residual_evals;    /* sum over scored models of n */
+    uint32_t lm_solves, lm_iterations;
+} mp_stats;
+
+typedef struct mp_ctx mp_ctx;
+
+const char *mp_last_error(void);
+int mp_create(int device, mp_ctx **out);
+void mp_destroy(mp_ctx *ctx);
+/* sm count, max SM clock (kHz), measured register-only FFMA / DFMA peaks (TFLOP/s) */
+int mp_device_info(mp_ctx *ctx, int *sm_count, int *sm_clock_khz);
+int mp_measure_alu_peaks(mp_ctx *ctx, double *fp32_tflops, double *fp64_tflops);
+
+/* ---- whole path: replaces HybridEstimatePoseScaleOffset{,SharedFocal,TwoFocal}
+ * (hybrid_pose_estimator.cpp:8-35, ...shared_focal....cpp:8-51, ...two_focal....cpp:34-75)
+ * for a batch of pairs.  out_inliers: caller buffer of sum_p 3*n_p int32; pair p's
+ * list for data type t starts at 3*(n_0+...+n_{p-1}) + t*n_p. */
+int mp_estimate_batch(mp_ctx *ctx, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
+                      const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers);
+/* device time (ms, CUDA events on the launching stream) of the kernels of the last
+ * mp_estimate_batch call, and the number of kernel launches it made */
+int mp_last_timing(mp_ctx *ctx, double *kernel_ms, double *total_ms, int *launches);
+
+/* ---- per-subsystem entry points (same kernels' device code, used by the parity tests) */
+/* ScoreModel (hybrid_ransac.h:265-282) over many models of one pair.
+ * scores_f32: fused fp32 scoring kernel; scores_f64: exact fp64 evaluation. Either may be NULL. */
+int mp_score_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
+                   int n_models, const mp_model *models, float *scores_f32, double *scores_f64);
+/* GetInliers (hybrid_ransac.h:289-349): ascending indices with r^2 < thr[t] (thr in
+ * the front-end's rescaled units, 3 entries); out_idx has 3*n entries (type t at t*n). */
+int mp_inliers(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
+               const mp_model *model, const double *thr3, int32_t *out_idx, int32_t *out_counts3);
+/* MinimalSolver (hybrid_pose_estimator.cpp:65-187 etc.) on explicit samples:
+ * sample_idx = n_samples x k (k = 3/4/4 for solver 0, 5/6/7 for solver 1);
+ * out_models = n_samples x max_models (4/8/4 or 10/15/3); models are in the
+ * front-end's internal (pp-subtracted, normalised) units. */
+int mp_minimal_solve_batch(mp_ctx *ctx, int kind, int solver_idx, const mp_pair *pair, const mp_options *opt,
+                           const mp_config *cfg, int n_samples, const int32_t *sample_idx, mp_model *out_models,
+                           int32_t *out_counts);
+/* NonMinimalSolver / LeastSquares (optimizer.h:9-131,247-499): one LM problem per
+ * entry; problem j uses indices idx[off[3j+t] .. off[3j+t+1]) for data type t.
+ * out_info: per problem {iterations, termination, initial_cost, final_cost} as doubles. */
+int mp_lm_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
+                int n_problems, const mp_model *start, const int32_t *idx, const int32_t *off, mp_model *out_models,
+                double *out_info);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,9 @@
+"""madpose_b200 -- B200-native hybrid LO-RANSAC hot path of MADPose behind the reference's API.
+
+`from madpose_b200 import *` exposes the pybind11 module (same names as `madpose`) once it is built;
+`madpose_b200.capi` is the ctypes view of the C ABI.  There is no CPU fallback."""
+try:  # the drop-in module (csrc/bindings.cpp); absent until built
+    from ._madpose import *  # noqa: F401,F403
+    HAVE_BINDINGS = True
+except ImportError:  # pragma: no cover
+    HAVE_BINDINGS = False

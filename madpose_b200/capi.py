@@ -1,0 +1,199 @@
+"""ctypes mirror of include/madpose_b200.h (the C ABI of libmadpose_b200.so).
+
+This is the thin Python view of the boundary used by the tests, bench.py and
+smoke(); the user-facing drop-in API is the pybind11 module built from
+csrc/bindings.cpp (same names as /root/reference/src/bindings.cpp:78-174).
+There is no CPU path: loading fails loudly when the CUDA library is missing and
+every call fails loudly when no sm_100 device is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmadpose_b200.so")
+
+KIND_CALIBRATED, KIND_SHARED_FOCAL, KIND_TWO_FOCAL = 0, 1, 2
+MODEL_DOUBLES = 17
+_dp = C.POINTER(C.c_double)
+
+
+class Options(C.Structure):
+    """madpose.HybridLORansacOptions (src/hybrid_ransac.h:17-25 + RansacLib defaults)."""
+
+    _fields_ = [
+        ("min_num_iterations", C.c_uint32), ("max_num_iterations", C.c_uint32),
+        ("max_num_iterations_per_solver", C.c_uint32), ("random_seed", C.c_uint32),
+        ("success_probability", C.c_double), ("squared_inlier_thresholds", C.c_double * 2),
+        ("data_type_weights", C.c_double * 2), ("threshold_multiplier", C.c_double),
+        ("num_lo_steps", C.c_int32), ("num_lsq_iterations", C.c_int32),
+        ("min_sample_multiplicator", C.c_int32), ("non_min_sample_multiplier", C.c_int32),
+        ("lo_starting_iterations", C.c_uint32), ("final_least_squares", C.c_int32),
+        ("use_ours", C.c_int32), ("use_4p4d", C.c_int32),
+    ]
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.min_num_iterations, self.max_num_iterations = 100, 10000
+        self.max_num_iterations_per_solver, self.random_seed = 10000, 0
+        self.success_probability = 0.9999
+        self.threshold_multiplier = 2.0 ** 0.5
+        self.num_lo_steps, self.num_lsq_iterations = 10, 4
+        self.min_sample_multiplicator, self.non_min_sample_multiplier = 7, 3
+        self.lo_starting_iterations, self.final_least_squares = 50, 0
+        for k, v in kw.items():
+            if k in ("squared_inlier_thresholds", "data_type_weights"):
+                getattr(self, k)[0], getattr(self, k)[1] = float(v[0]), float(v[1])
+            else:
+                setattr(self, k, v)
+
+
+class Config(C.Structure):
+    """madpose.EstimatorConfig (src/estimator_config.h:5-33)."""
+
+    _fields_ = [
+        ("solver_type", C.c_int32), ("score_type", C.c_int32), ("lo_type", C.c_int32),
+        ("min_depth_constraint", C.c_int32), ("use_shift", C.c_int32),
+        ("ceres_use_nonmonotonic_steps", C.c_int32), ("ceres_num_threads", C.c_int32), ("reserved_", C.c_int32),
+        ("ceres_function_tolerance", C.c_double), ("ceres_gradient_tolerance", C.c_double),
+        ("ceres_parameter_tolerance", C.c_double), ("ceres_max_num_iterations", C.c_double),
+    ]
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.min_depth_constraint, self.use_shift = 1, 1
+        self.ceres_use_nonmonotonic_steps, self.ceres_num_threads = 1, 1
+        self.ceres_function_tolerance, self.ceres_gradient_tolerance = 1e-6, 1e-8
+        self.ceres_parameter_tolerance, self.ceres_max_num_iterations = 1e-6, 25
+        for k, v in kw.items():
+            setattr(self, k, v)
+
+
+class Pair(C.Structure):
+    _fields_ = [
+        ("n", C.c_int32), ("reserved_", C.c_int32),
+        ("x0", _dp), ("x1", _dp), ("d0", _dp), ("d1", _dp),
+        ("min_depth", C.c_double * 2), ("K0", C.c_double * 9), ("K1", C.c_double * 9),
+        ("pp0", C.c_double * 2), ("pp1", C.c_double * 2),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("num_iterations_total", C.c_uint32), ("num_iterations_per_solver", C.c_uint32 * 2),
+        ("best_num_inliers", C.c_int32), ("best_solver_type", C.c_int32), ("number_lo_iterations", C.c_int32),
+        ("num_inliers", C.c_int32 * 3), ("reserved_", C.c_int32),
+        ("best_model_score", C.c_double), ("inlier_ratios", C.c_double * 3),
+        ("hypotheses_scored", C.c_uint64), ("residual_evals", C.c_uint64),
+        ("lm_solves", C.c_uint32), ("lm_iterations", C.c_uint32),
+    ]
+
+
+def make_pair(x0, x1, d0, d1, min_depth, K0=None, K1=None, pp0=None, pp1=None):
+    """Builds an mp_pair over contiguous float64 copies; returns (Pair, keepalive)."""
+    a = [np.ascontiguousarray(v, dtype=np.float64) for v in (x0, x1, d0, d1)]
+    n = a[2].shape[0]
+    assert a[0].shape == (n, 2) and a[1].shape == (n, 2) and a[3].shape == (n,), "x: (n,2), depth: (n,)"
+    p = Pair()
+    p.n = n
+    p.x0, p.x1, p.d0, p.d1 = (v.ctypes.data_as(_dp) for v in a)
+    p.min_depth[0], p.min_depth[1] = float(min_depth[0]), float(min_depth[1])
+    eye = np.eye(3)
+    for dst, src in ((p.K0, K0), (p.K1, K1)):
+        m = np.asarray(eye if src is None else src, dtype=np.float64).reshape(9)
+        for i in range(9):
+            dst[i] = m[i]
+    for dst, src in ((p.pp0, pp0), (p.pp1, pp1)):
+        v = np.zeros(2) if src is None else np.asarray(src, dtype=np.float64).reshape(2)
+        dst[0], dst[1] = v[0], v[1]
+    return p, a
+
+
+def models_to_array(models):
+    m = np.ascontiguousarray(models, dtype=np.float64)
+    assert m.ndim == 2 and m.shape[1] == MODEL_DOUBLES
+    return m
+
+
+def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
+    return np.concatenate([np.asarray(R, float).reshape(9), np.asarray(t, float).reshape(3), [scale, o0, o1, f0, f1]])
+
+
+_SYMBOLS = [
+    "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
+    "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
+]
+
+
+def load_library(path=LIB_PATH):
+    if not os.path.exists(path):
+        raise ImportError(f"{path} missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(madpose_b200 has no CPU fallback)")
+    lib = C.CDLL(path)
+    for s in _SYMBOLS:
+        getattr(lib, s)  # AttributeError if the library does not export the full ABI
+    lib.mp_last_error.restype = C.c_char_p
+    for s in _SYMBOLS[1:]:
+        getattr(lib, s).restype = C.c_int
+    lib.mp_destroy.restype = None
+    return lib
+
+
+class Context:
+    """Owns an mp_ctx on one GPU."""
+
+    def __init__(self, device=0, lib=None):
+        self.lib = lib or load_library()
+        self.ctx = C.c_void_p()
+        self._check(self.lib.mp_create(int(device), C.byref(self.ctx)))
+
+    def _check(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"madpose_b200 error {rc}: {self.lib.mp_last_error().decode()}")
+
+    def close(self):
+        if self.ctx:
+            self.lib.mp_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def device_info(self):
+        sm, khz = C.c_int(), C.c_int()
+        self._check(self.lib.mp_device_info(self.ctx, C.byref(sm), C.byref(khz)))
+        return sm.value, khz.value
+
+    def measure_alu_peaks(self):
+        a, b = C.c_double(), C.c_double()
+        self._check(self.lib.mp_measure_alu_peaks(self.ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def last_timing(self):
+        k, t, n = C.c_double(), C.c_double(), C.c_int()
+        self._check(self.lib.mp_last_timing(self.ctx, C.byref(k), C.byref(t), C.byref(n)))
+        return k.value, t.value, n.value
+
+    def score_batch(self, kind, pair, opt, cfg, models, want32=True, want64=True):
+        m = models_to_array(models)
+        nm = m.shape[0]
+        s32 = np.zeros(nm, np.float32) if want32 else None
+        s64 = np.zeros(nm, np.float64) if want64 else None
+        self._check(self.lib.mp_score_batch(
+            self.ctx, kind, C.byref(pair), C.byref(opt), C.byref(cfg), nm, m.ctypes.data_as(C.c_void_p),
+            s32.ctypes.data_as(C.c_void_p) if want32 else None, s64.ctypes.data_as(C.c_void_p) if want64 else None))
+        return s32, s64
+
+    def inliers(self, kind, pair, opt, cfg, model, thr3):
+        m = np.ascontiguousarray(model, np.float64).reshape(MODEL_DOUBLES)
+        thr = np.ascontiguousarray(thr3, np.float64).reshape(3)
+        idx = np.zeros(3 * pair.n, np.int32)
+        cnt = np.zeros(3, np.int32)
+        self._check(self.lib.mp_inliers(self.ctx, kind, C.byref(pair), C.byref(opt), C.byref(cfg),
+                                        m.ctypes.data_as(C.c_void_p), thr.ctypes.data_as(C.c_void_p),
+                                        idx.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p)))
+        return [idx[t * pair.n: t * pair.n + cnt[t]].copy() for t in range(3)]

@@ -1,0 +1,160 @@
+// C ABI of madpose_b200 (include/madpose_b200.h).  Every entry point runs CUDA
+// kernels on the context's device; there is no CPU fallback.
+#include "mp_host.cuh"
+#include "mp_capi_more.cuh"
+
+namespace mp {
+thread_local std::string g_err;
+}
+using namespace mp;
+
+extern "C" {
+
+const char *mp_last_error(void) { return g_err.c_str(); }
+
+int mp_create(int device, mp_ctx **out) {
+    if (!out) return fail(MP_ERR_ARG, "mp_create: out is null");
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail(MP_ERR_NO_DEVICE, "no CUDA device: madpose_b200 has no CPU path");
+    if (device < 0 || device >= count) return fail(MP_ERR_ARG, "device index out of range");
+    cudaDeviceProp prop;
+    MP_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(MP_ERR_NO_DEVICE, "device is not sm_100 (B200) class");
+    MP_CUDA(cudaSetDevice(device));
+    mp_ctx *c = new mp_ctx();
+    c->device = device; c->sm_count = prop.multiProcessorCount; c->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
+    c->clock_khz = khz;
+    MP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (auto &e : c->ev) MP_CUDA(cudaEventCreate(&e));
+    *out = c;
+    return MP_OK;
+}
+
+void mp_destroy(mp_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int mp_device_info(mp_ctx *c, int *sm_count, int *sm_clock_khz) {
+    if (!c) return fail(MP_ERR_ARG, "null context");
+    if (sm_count) *sm_count = c->sm_count;
+    if (sm_clock_khz) *sm_clock_khz = c->clock_khz;
+    return MP_OK;
+}
+
+int mp_measure_alu_peaks(mp_ctx *c, double *fp32_tflops, double *fp64_tflops) {
+    if (!c) return fail(MP_ERR_ARG, "null context");
+    MP_CUDA(cudaSetDevice(c->device));
+    MP_CUDA(c->d_misc.reserve(64));
+    const int blocks = c->sm_count * 8, threads = 256;
+    float ms = 0;
+    for (int pass = 0; pass < 2; pass++) { // pass 0 warms up
+        const int it32 = 20000, it64 = 4000;
+        MP_CUDA(cudaEventRecord(c->ev[0], c->stream));
+        ffma_peak_kernel<<<blocks, threads, 0, c->stream>>>(c->d_misc.as<float>(), it32);
+        MP_CUDA(cudaEventRecord(c->ev[1], c->stream));
+        dfma_peak_kernel<<<blocks, threads, 0, c->stream>>>(c->d_misc.as<double>(), it64);
+        MP_CUDA(cudaEventRecord(c->ev[2], c->stream));
+        MP_CUDA(cudaStreamSynchronize(c->stream));
+        MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+        if (fp32_tflops) *fp32_tflops = 2.0 * 8 * it32 * (double)blocks * threads / (ms * 1e-3) / 1e12;
+        MP_CUDA(cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]));
+        if (fp64_tflops) *fp64_tflops = 2.0 * 8 * it64 * (double)blocks * threads / (ms * 1e-3) / 1e12;
+    }
+    return MP_OK;
+}
+
+int mp_last_timing(mp_ctx *c, double *kernel_ms, double *total_ms, int *launches) {
+    if (!c) return fail(MP_ERR_ARG, "null context");
+    if (kernel_ms) *kernel_ms = c->last_kernel_ms;
+    if (total_ms) *total_ms = c->last_total_ms;
+    if (launches) *launches = c->last_launches;
+    return MP_OK;
+}
+
+int mp_score_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int nm,
+                   const mp_model *models, float *s32, double *s64) {
+    if (!c || !pair || !opt || !cfg || !models || nm <= 0) return fail(MP_ERR_ARG, "mp_score_batch: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    int rc = upload_pairs(c, kind, 1, pair, opt);
+    if (rc) return rc;
+    MP_CUDA(c->d_models.reserve(nm * sizeof(Model)));
+    MP_CUDA(c->d_hyps.reserve(nm * sizeof(HypF)));
+    MP_CUDA(c->d_scores32.reserve(nm * sizeof(float)));
+    MP_CUDA(c->d_scores64.reserve(nm * sizeof(double)));
+    MP_CUDA(cudaMemcpyAsync(c->d_models.p, models, nm * sizeof(Model), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    int launches = 1;
+    if (s32) {
+        pack_hyps_kernel<<<(nm + 255) / 256, 256, 0, s>>>(kind, nm, c->d_models.as<Model>(), c->d_hyps.as<HypF>());
+        int cap = (c->smem_optin - 2048) / 32;
+        cap = std::min(cap, std::max(pair->n, 32));
+        cap = (cap + 31) / 32 * 32;
+        size_t smem = (size_t)cap * 32;
+        int groups = (nm + MP_HT - 1) / MP_HT;
+        int grid = std::max(1, std::min(c->sm_count, (groups + MP_WARPS - 1) / MP_WARPS));
+        auto launch = [&](auto kern) -> cudaError_t {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            kern<<<grid, MP_CTA, smem, s>>>(c->d_pc.as<PairConst>(), c->d_s32.as<float4>(), cfg->score_type, nm,
+                                            c->d_hyps.as<HypF>(), c->d_scores32.as<float>(), cap);
+            return cudaGetLastError();
+        };
+        if (kind == CALIB) MP_CUDA(launch(score_f32_kernel<CALIB>));
+        else if (kind == SHARED) MP_CUDA(launch(score_f32_kernel<SHARED>));
+        else MP_CUDA(launch(score_f32_kernel<TWO>));
+        launches += 2;
+    }
+    MP_CUDA(cudaEventRecord(c->ev[2], s));
+    if (s64) {
+        score_f64_kernel<<<std::min(nm, c->sm_count * 8), 256, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(),
+                                                                        cfg->score_type, nm, c->d_models.as<Model>(),
+                                                                        c->d_scores64.as<double>());
+        MP_CUDA(cudaGetLastError());
+        launches += 1;
+    }
+    if (s32) MP_CUDA(cudaMemcpyAsync(s32, c->d_scores32.p, nm * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (s64) MP_CUDA(cudaMemcpyAsync(s64, c->d_scores64.p, nm * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaEventRecord(c->ev[3], s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float k = 0, t = 0;
+    MP_CUDA(cudaEventElapsedTime(&k, c->ev[1], c->ev[2])); // fp32 scoring (pack + fused kernel)
+    MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));
+    c->last_kernel_ms = k; c->last_total_ms = t; c->last_launches = launches;
+    return MP_OK;
+}
+
+int mp_inliers(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
+               const mp_model *model, const double *thr3, int32_t *out_idx, int32_t *out_counts3) {
+    if (!c || !pair || !opt || !cfg || !model || !thr3 || !out_idx || !out_counts3)
+        return fail(MP_ERR_ARG, "mp_inliers: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    int rc = upload_pairs(c, kind, 1, pair, opt);
+    if (rc) return rc;
+    const int n = pair->n;
+    MP_CUDA(c->d_models.reserve(sizeof(Model)));
+    MP_CUDA(c->d_misc.reserve(64));
+    MP_CUDA(c->d_idx.reserve((3 * (size_t)n + 4) * sizeof(int)));
+    MP_CUDA(cudaMemcpyAsync(c->d_models.p, model, sizeof(Model), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(c->d_misc.p, thr3, 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+    inliers_kernel<<<1, MP_CTA, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), c->d_models.as<Model>(),
+                                        c->d_misc.as<double>(), c->d_idx.as<int>(), c->d_idx.as<int>() + 3 * n);
+    MP_CUDA(cudaGetLastError());
+    MP_CUDA(cudaMemcpyAsync(out_idx, c->d_idx.p, 3 * (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(out_counts3, c->d_idx.as<int>() + 3 * n, 3 * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    return MP_OK;
+}
+
+} // extern "C"
