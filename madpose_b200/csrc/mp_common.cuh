@@ -83,7 +83,7 @@ MP_HD bool inv3(const double *A, double *B) {
 }
 MP_HD bool finite_d(double v) { return fabs(v) <= DBL_MAX; }
 MP_HD bool model_finite(const Model &m) {
-    const double *p = m.R;
+    const double *p = reinterpret_cast<const double *>(&m);
     bool ok = true;
     for (int i = 0; i < MP_MODEL_DOUBLES; i++) ok = ok && finite_d(p[i]);
     return ok;

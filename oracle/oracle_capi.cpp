@@ -2,6 +2,10 @@
 // CPU restatement through ctypes.  Nothing here is linked into the product.
 #include "om_affine.h"
 #include "om_estimator.h"
+#include "om_minimal.h"
+#include "om_lm.h"
+#include "om_ransac.h"
+#include <thread>
 
 extern "C" {
 
@@ -65,6 +69,79 @@ int om_frontend(int kind, const mp_pair *pair, const mp_options *opt, const mp_c
     om::make_problem(kind, *pair, *opt, *cfg, &P);
     out8[0] = P.norm_scale; out8[1] = P.thr[0]; out8[2] = P.thr[1]; out8[3] = P.thr[2];
     out8[4] = P.w[0]; out8[5] = P.w[1]; out8[6] = P.w[2]; out8[7] = P.loss_scale;
+    return 0;
+}
+
+// MinimalSolver on explicit samples; out_models: n_samples x max_models
+int om_minimal_solve(int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int solver_idx,
+                     int n_samples, const int *idx, int max_models, mp_model *out_models, int *out_counts) {
+    om::Problem P;
+    om::make_problem(kind, *pair, *opt, *cfg, &P);
+    int k = solver_idx == 0 ? P.sizes[0][0] : P.sizes[1][2];
+    std::vector<om::Model> models;
+    for (int s = 0; s < n_samples; s++) {
+        om::minimal_solver(P, solver_idx, idx + (size_t)s * k, &models);
+        int c = std::min((int)models.size(), max_models);
+        out_counts[s] = c;
+        for (int j = 0; j < c; j++) std::memcpy(out_models + (size_t)s * max_models + j, &models[j], sizeof(mp_model));
+    }
+    return 0;
+}
+
+// NonMinimalSolver / LeastSquares: problem j uses idx[off[3j+t] .. off[3j+t+1]) for type t
+int om_lm(int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int n_problems,
+          const mp_model *start, const int *idx, const int *off, mp_model *out_models, double *out_info) {
+    om::Problem P;
+    om::make_problem(kind, *pair, *opt, *cfg, &P);
+    for (int j = 0; j < n_problems; j++) {
+        std::vector<int> s[3];
+        for (int t = 0; t < 3; t++) s[t].assign(idx + off[3 * j + t], idx + off[3 * j + t + 1]);
+        om::Model m = *reinterpret_cast<const om::Model *>(start + j);
+        om::LmInfo info;
+        om::lm_solve(P, s, &m, &info);
+        std::memcpy(out_models + j, &m, sizeof(mp_model));
+        out_info[4 * j] = info.iterations; out_info[4 * j + 1] = info.termination;
+        out_info[4 * j + 2] = info.cost0; out_info[4 * j + 3] = info.cost;
+    }
+    return 0;
+}
+
+static void fill_stats(const om::Stats &st, int n, mp_stats *o, int *inl) {
+    std::memset(o, 0, sizeof(*o));
+    o->num_iterations_total = st.num_iterations_total;
+    o->num_iterations_per_solver[0] = st.num_iterations_per_solver[0];
+    o->num_iterations_per_solver[1] = st.num_iterations_per_solver[1];
+    o->best_num_inliers = st.best_num_inliers; o->best_solver_type = st.best_solver_type;
+    o->number_lo_iterations = st.number_lo_iterations; o->best_model_score = st.best_model_score;
+    for (int t = 0; t < 3; t++) {
+        o->inlier_ratios[t] = st.inlier_ratios[t];
+        o->num_inliers[t] = t < (int)st.inlier_indices.size() ? (int)st.inlier_indices[t].size() : 0;
+        if (inl) for (int k = 0; k < o->num_inliers[t]; k++) inl[t * n + k] = st.inlier_indices[t][k];
+    }
+    o->hypotheses_scored = st.hypotheses_scored; o->residual_evals = st.residual_evals;
+    o->lm_solves = st.lm_solves; o->lm_iterations = st.lm_iterations;
+}
+
+// whole path for a batch of pairs on `threads` host threads (pair p -> thread p % threads).
+// out_inliers layout = mp_estimate_batch.  trace (optional, pair 0 only): up to trace_cap doubles.
+int om_estimate_batch(int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt, const mp_config *cfg,
+                      mp_model *out_models, mp_stats *out_stats, int *out_inliers, int threads, double *trace,
+                      int trace_cap) {
+    std::vector<long long> off(n_pairs + 1, 0);
+    for (int p = 0; p < n_pairs; p++) off[p + 1] = off[p] + 3ll * pairs[p].n;
+    auto work = [&](int tid) {
+        for (int p = tid; p < n_pairs; p += threads) {
+            om::Model m; om::Stats st; om::Trace tr;
+            om::estimate(kind, pairs[p], *opt, *cfg, &m, &st, (p == 0 && trace) ? &tr : nullptr);
+            std::memcpy(out_models + p, &m, sizeof(mp_model));
+            fill_stats(st, pairs[p].n, out_stats + p, out_inliers ? out_inliers + off[p] : nullptr);
+            if (p == 0 && trace) for (int i = 0; i < trace_cap; i++) trace[i] = i < (int)tr.size() ? tr[i] : -1.0;
+        }
+    };
+    if (threads <= 1) { threads = 1; work(0); return 0; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++) th.emplace_back(work, t);
+    for (auto &t : th) t.join();
     return 0;
 }
 

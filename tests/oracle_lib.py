@@ -46,6 +46,46 @@ class Oracle:
                             _ptr(idx), _ptr(cnt))
         return [idx[k * pair.n: k * pair.n + cnt[k]].copy() for k in range(3)]
 
+    def minimal_solve(self, kind, pair, opt, cfg, solver_idx, samples, max_models=15):
+        idx = np.ascontiguousarray(samples, np.int32)
+        ns = idx.shape[0]
+        out = np.zeros((ns, max_models, 17)); cnt = np.zeros(ns, np.int32)
+        self.lib.om_minimal_solve(kind, C.byref(pair), C.byref(opt), C.byref(cfg), solver_idx, ns, _ptr(idx),
+                                  max_models, _ptr(out), _ptr(cnt))
+        return [out[i, :cnt[i]].copy() for i in range(ns)]
+
+    def lm(self, kind, pair, opt, cfg, starts, samples):
+        """samples: list (per problem) of 3 index arrays."""
+        st = np.ascontiguousarray(starts, np.float64).reshape(-1, 17)
+        flat, off = [], [0]
+        for s3 in samples:
+            for t in range(3):
+                flat.extend(int(v) for v in s3[t]); off.append(len(flat))
+        idx = np.array(flat + [0], np.int32); off = np.array(off, np.int32)
+        out = np.zeros_like(st); info = np.zeros((st.shape[0], 4))
+        self.lib.om_lm(kind, C.byref(pair), C.byref(opt), C.byref(cfg), st.shape[0], _ptr(st), _ptr(idx), _ptr(off),
+                       _ptr(out), _ptr(info))
+        return out, info
+
+    def estimate_batch(self, kind, pairs, opt, cfg, threads=1, trace_cap=0, lib=None):
+        """pairs: list of capi.Pair.  Returns (models (P,17), list of capi.Stats, list of 3 inlier arrays[, trace])."""
+        from madpose_b200 import capi
+        lib = lib or self.lib
+        n = len(pairs)
+        arr = (capi.Pair * n)(*pairs)
+        models = np.zeros((n, 17)); stats = (capi.Stats * n)()
+        tot = sum(p.n for p in pairs)
+        inl = np.zeros(3 * tot + 1, np.int32)
+        tr = np.zeros(max(trace_cap, 1))
+        fn = lib.om_estimate_batch if hasattr(lib, "om_estimate_batch") else lib.omref_estimate_batch
+        fn(kind, n, arr, C.byref(opt), C.byref(cfg), _ptr(models), stats, _ptr(inl), threads,
+           _ptr(tr) if trace_cap else None, trace_cap)
+        out, o = [], 0
+        for p, s in zip(pairs, stats):
+            out.append([inl[o + t * p.n: o + t * p.n + s.num_inliers[t]].copy() for t in range(3)])
+            o += 3 * p.n
+        return (models, list(stats), out, tr) if trace_cap else (models, list(stats), out)
+
     def frontend(self, kind, pair, opt, cfg):
         o = np.zeros(8)
         self.lib.om_frontend(kind, C.byref(pair), C.byref(opt), C.byref(cfg), _ptr(o))
