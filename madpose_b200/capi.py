@@ -197,3 +197,44 @@ class Context:
                                         m.ctypes.data_as(C.c_void_p), thr.ctypes.data_as(C.c_void_p),
                                         idx.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p)))
         return [idx[t * pair.n: t * pair.n + cnt[t]].copy() for t in range(3)]
+
+    def minimal_solve_batch(self, kind, pair, opt, cfg, solver_idx, samples):
+        """samples: (n_samples, k) int32.  Returns a list of (count, 17) arrays in the front-end's internal units."""
+        idx = np.ascontiguousarray(samples, np.int32)
+        ns = idx.shape[0]
+        mm = ([4, 8, 4] if solver_idx == 0 else [10, 15, 3])[kind]
+        out = np.zeros((ns, mm, MODEL_DOUBLES)); cnt = np.zeros(ns, np.int32)
+        self._check(self.lib.mp_minimal_solve_batch(self.ctx, kind, solver_idx, C.byref(pair), C.byref(opt), C.byref(cfg),
+                                                    ns, idx.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
+                                                    cnt.ctypes.data_as(C.c_void_p)))
+        return [out[i, :cnt[i]].copy() for i in range(ns)]
+
+    def lm_batch(self, kind, pair, opt, cfg, starts, samples):
+        """samples: per problem a list of 3 index arrays.  Returns (models (P,17), info (P,4))."""
+        st = np.ascontiguousarray(starts, np.float64).reshape(-1, MODEL_DOUBLES)
+        flat, off = [], [0]
+        for s3 in samples:
+            for t in range(3):
+                flat.extend(int(v) for v in s3[t]); off.append(len(flat))
+        idx = np.array(flat + [0], np.int32); off = np.array(off, np.int32)
+        out = np.zeros_like(st); info = np.zeros((st.shape[0], 4))
+        self._check(self.lib.mp_lm_batch(self.ctx, kind, C.byref(pair), C.byref(opt), C.byref(cfg), st.shape[0],
+                                         st.ctypes.data_as(C.c_void_p), idx.ctypes.data_as(C.c_void_p),
+                                         off.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
+                                         info.ctypes.data_as(C.c_void_p)))
+        return out, info
+
+    def estimate_batch(self, kind, pairs, opt, cfg):
+        """pairs: list of Pair.  Returns (models (P,17), list of Stats, list of 3 inlier index arrays per pair)."""
+        n = len(pairs)
+        arr = (Pair * n)(*pairs)
+        models = np.zeros((n, MODEL_DOUBLES)); stats = (Stats * n)()
+        tot = sum(p.n for p in pairs)
+        inl = np.zeros(3 * tot + 1, np.int32)
+        self._check(self.lib.mp_estimate_batch(self.ctx, kind, n, arr, C.byref(opt), C.byref(cfg),
+                                               models.ctypes.data_as(C.c_void_p), stats, inl.ctypes.data_as(C.c_void_p)))
+        out, o = [], 0
+        for p, s in zip(pairs, stats):
+            out.append([inl[o + t * p.n: o + t * p.n + s.num_inliers[t]].copy() for t in range(3)])
+            o += 3 * p.n
+        return models, list(stats), out

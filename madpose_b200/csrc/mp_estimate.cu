@@ -1,0 +1,190 @@
+// Whole-path translation unit: mp_estimate_batch (host side of the device loop) and mp_lm_batch.
+#include "mp_estimate.cuh"
+#include "mp_loop_kernels.cuh"
+#include <algorithm>
+
+namespace mp {
+
+// PairState -> mp_model / mp_stats; undoes the focal normalisation
+// (...shared_focal_estimator.cpp:49, ...two_focal_estimator.cpp:72-73)
+__global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp_stats *stats) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pairs) return;
+    const PairState &S = L.st[p];
+    const PairConst &pc = L.pc[p];
+    Model m = S.best;
+    if (pc.kind == SHARED) { m.f0 *= pc.norm_scale; m.f1 = m.f0; }
+    if (pc.kind == TWO) { m.f0 *= pc.norm_scale; m.f1 *= pc.norm_scale; }
+    *reinterpret_cast<Model *>(models + p) = m;
+    mp_stats o;
+    o.num_iterations_total = S.total;
+    o.num_iterations_per_solver[0] = S.iters[0]; o.num_iterations_per_solver[1] = S.iters[1];
+    o.best_num_inliers = S.best_num_inliers; o.best_solver_type = S.best_solver; o.number_lo_iterations = S.number_lo;
+    for (int t = 0; t < 3; t++) { o.num_inliers[t] = S.num_inl[t]; o.inlier_ratios[t] = S.ratios[t]; }
+    o.reserved_ = 0;
+    o.best_model_score = S.best_score;
+    o.hypotheses_scored = S.hyps_scored; o.residual_evals = S.evals; o.lm_solves = S.lm_solves; o.lm_iterations = S.lm_iters;
+    stats[p] = o;
+}
+
+static int run_estimate(mp_ctx *c, LoopAlloc &A, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
+                        const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers) {
+    if (opt->use_ours || opt->use_4p4d) return fail(MP_ERR_ARG, "use_ours / use_4p4d solvers are not implemented");
+    if (opt->num_lsq_iterations < 0 || opt->num_lo_steps < 0 || opt->min_sample_multiplicator < 0)
+        return fail(MP_ERR_ARG, "negative LO option");
+    cudaStream_t s = c->stream;
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    int rc = upload_pairs(c, kind, n_pairs, pairs, opt);
+    if (rc) return rc;
+    const long long N = c->total_n;
+    // per-pair scratch capacities
+    MP_CUDA(A.h_off3.reserve((n_pairs + 1) * sizeof(long long)));
+    MP_CUDA(A.h_caps.reserve(n_pairs * sizeof(int)));
+    long long *off3 = A.h_off3.as<long long>();
+    int *caps = A.h_caps.as<int>();
+    const int k0 = kind == CALIB ? 3 : 4, k2 = kind == CALIB ? 5 : (kind == SHARED ? 6 : 7);
+    const long long mult = opt->min_sample_multiplicator;
+    const long long total_upper = std::max<long long>(2 * k0, k2) * mult * mult;
+    off3[0] = 0;
+    int max_n = 32;
+    for (int p = 0; p < n_pairs; p++) {
+        long long cap = 3ll * pairs[p].n + std::max<long long>(total_upper, 64) + 64;
+        if (cap > 2000000000ll) return fail(MP_ERR_ARG, "pair too large");
+        caps[p] = (int)cap;
+        off3[p + 1] = off3[p] + cap;
+        max_n = std::max(max_n, pairs[p].n);
+    }
+    const long long CAP = off3[n_pairs];
+    const size_t slots = (size_t)n_pairs * LP_BMAX * LP_MM;
+    MP_CUDA(A.st.reserve(n_pairs * sizeof(PairState)));
+    MP_CUDA(A.wk.reserve(n_pairs * sizeof(PairWork)));
+    MP_CUDA(A.rngA.reserve(n_pairs * sizeof(MtStream)));
+    MP_CUDA(A.rngB.reserve(n_pairs * sizeof(MtStream)));
+    MP_CUDA(A.models.reserve(slots * sizeof(Model)));
+    MP_CUDA(A.hyps.reserve(slots * sizeof(HypF)));
+    MP_CUDA(A.inl_best.reserve((3 * (size_t)N + 4) * sizeof(int)));
+    MP_CUDA(A.inl_cur.reserve((3 * (size_t)N + 4) * sizeof(int)));
+    MP_CUDA(A.flat.reserve(2 * (size_t)CAP * sizeof(int)));
+    MP_CUDA(A.sample.reserve(3 * (size_t)CAP * sizeof(int)));
+    MP_CUDA(A.misc.reserve(64));
+    MP_CUDA(A.off3.reserve((n_pairs + 1) * sizeof(long long)));
+    MP_CUDA(A.caps.reserve(n_pairs * sizeof(int)));
+    MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
+    MP_CUDA(A.out_models.reserve(n_pairs * sizeof(mp_model)));
+    MP_CUDA(A.out_stats.reserve(n_pairs * sizeof(mp_stats)));
+    MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
+    MP_CUDA(A.h_active.reserve(64));
+    LoopParams *prm = A.h_prm.as<LoopParams>();
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = LP_BMAX; prm->guard = 1e-3;
+    int *h_active = A.h_active.as<int>();
+    *h_active = n_pairs;
+    MP_CUDA(cudaMemcpyAsync(A.prm.p, prm, sizeof(LoopParams), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(A.off3.p, off3, (n_pairs + 1) * sizeof(long long), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(A.caps.p, caps, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(A.misc.p, h_active, sizeof(int), cudaMemcpyHostToDevice, s));
+    LoopBuffers L;
+    L.pc = c->d_pc.as<PairConst>(); L.M = c->d_m64.as<Match64>(); L.S32 = c->d_s32.as<float4>();
+    L.st = A.st.as<PairState>(); L.wk = A.wk.as<PairWork>(); L.rngA = A.rngA.as<MtStream>(); L.rngB = A.rngB.as<MtStream>();
+    L.models = A.models.as<Model>(); L.hyps = A.hyps.as<HypF>();
+    L.inl_best = A.inl_best.as<int>(); L.inl_cur = A.inl_cur.as<int>(); L.flat = A.flat.as<int>(); L.sample = A.sample.as<int>();
+    L.n_active = A.misc.as<int>();
+    const LoopParams *dprm = A.prm.as<LoopParams>();
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    init_state_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, dprm);
+    MP_CUDA(cudaGetLastError());
+    int launches = 2;
+    int tile_cap = (c->smem_optin - 4096) / 32;
+    tile_cap = std::min(tile_cap, (max_n + 31) / 32 * 32);
+    tile_cap = tile_cap / 32 * 32;
+    const size_t smem = (size_t)tile_cap * 32;
+    const unsigned max_it = std::max(opt->max_num_iterations, opt->min_num_iterations);
+    const long long max_rounds = 2ll * max_it + 64;
+    long long rounds = 0;
+    while (true) {
+        MP_CUDA(cudaMemcpyAsync(h_active, A.misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        MP_CUDA(cudaStreamSynchronize(s));
+        if (*h_active <= 0) break;
+        if (++rounds > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
+        sample_kernel<<<(n_pairs + 31) / 32, 32, 0, s>>>(L, dprm);
+        MP_CUDA(launch_minimal_batch(L, dprm, n_pairs, s));
+        if (kind == CALIB) MP_CUDA(launch_round_kind<CALIB>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
+        else if (kind == SHARED) MP_CUDA(launch_round_kind<SHARED>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
+        else MP_CUDA(launch_round_kind<TWO>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
+        launches += 4;
+    }
+    finalize_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, n_pairs, A.out_models.as<mp_model>(), A.out_stats.as<mp_stats>());
+    MP_CUDA(cudaGetLastError());
+    launches += 1;
+    MP_CUDA(cudaEventRecord(c->ev[2], s));
+    MP_CUDA(cudaMemcpyAsync(out_models, A.out_models.p, n_pairs * sizeof(mp_model), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(out_stats, A.out_stats.p, n_pairs * sizeof(mp_stats), cudaMemcpyDeviceToHost, s));
+    if (out_inliers && N > 0)
+        MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, 3 * (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaEventRecord(c->ev[3], s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float k = 0, t = 0;
+    MP_CUDA(cudaEventElapsedTime(&k, c->ev[1], c->ev[2]));
+    MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));
+    c->last_kernel_ms = k; c->last_total_ms = t; c->last_launches = launches;
+    c->last_rounds = (int)rounds;
+    return MP_OK;
+}
+
+} // namespace mp
+
+extern "C" {
+int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int n_problems,
+                const mp_model *start, const int32_t *idx, const int32_t *off, mp_model *out_models, double *out_info) {
+    using namespace mp;
+    if (!c || !pair || !opt || !cfg || !start || !idx || !off || !out_models || !out_info || n_problems <= 0)
+        return fail(MP_ERR_ARG, "mp_lm_batch: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    int rc = upload_pairs(c, kind, 1, pair, opt);
+    if (rc) return rc;
+    const int nidx = off[3 * n_problems];
+    for (int i = 0; i < nidx; i++)
+        if (idx[i] < 0 || idx[i] >= pair->n) return fail(MP_ERR_ARG, "mp_lm_batch: index out of range");
+    if (!c->loop_alloc) c->loop_alloc = new LoopAlloc();
+    LoopAlloc &A = *static_cast<LoopAlloc *>(c->loop_alloc);
+    MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
+    MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
+    LoopParams *prm = A.h_prm.as<LoopParams>();
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = 1; prm->bmax = LP_BMAX; prm->guard = 1e-3;
+    MP_CUDA(c->d_models.reserve(2 * (size_t)n_problems * sizeof(Model)));
+    MP_CUDA(c->d_idx.reserve(((size_t)nidx + 3 * (size_t)n_problems + 8) * sizeof(int)));
+    MP_CUDA(c->d_scores64.reserve(4 * (size_t)n_problems * sizeof(double)));
+    Model *d_start = c->d_models.as<Model>(), *d_out = d_start + n_problems;
+    int *d_idx = c->d_idx.as<int>(), *d_off = d_idx + nidx + 1;
+    MP_CUDA(cudaMemcpyAsync(A.prm.p, prm, sizeof(LoopParams), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(d_start, start, n_problems * sizeof(Model), cudaMemcpyHostToDevice, s));
+    if (nidx > 0) MP_CUDA(cudaMemcpyAsync(d_idx, idx, nidx * sizeof(int), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(d_off, off, (3 * n_problems + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    const PairConst *pc = c->d_pc.as<PairConst>();
+    const Match64 *M = c->d_m64.as<Match64>();
+    const LoopParams *dprm = A.prm.as<LoopParams>();
+    double *d_info = c->d_scores64.as<double>();
+    if (kind == CALIB) MP_CUDA(launch_lm_kind<CALIB>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
+    else if (kind == SHARED) MP_CUDA(launch_lm_kind<SHARED>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
+    else MP_CUDA(launch_lm_kind<TWO>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    MP_CUDA(cudaMemcpyAsync(out_models, d_out, n_problems * sizeof(Model), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(out_info, d_info, 4 * (size_t)n_problems * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float ms = 0;
+    MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 2;
+    return MP_OK;
+}
+int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
+                      const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers) {
+    using namespace mp;
+    if (!c || !pairs || !opt || !cfg || !out_models || !out_stats || n_pairs <= 0)
+        return fail(MP_ERR_ARG, "mp_estimate_batch: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    if (!c->loop_alloc) c->loop_alloc = new LoopAlloc();
+    return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), kind, n_pairs, pairs, opt, cfg, out_models,
+                        out_stats, out_inliers);
+}
+}

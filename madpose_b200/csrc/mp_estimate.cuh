@@ -1,0 +1,21 @@
+// Launchers implemented in the other translation units + the per-context loop buffers.
+#pragma once
+#include "mp_host.cuh"
+#include "mp_loop.cuh"
+
+namespace mp {
+
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int n_pairs, cudaStream_t s);
+template <int KIND>
+cudaError_t launch_round_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, int tile_cap, size_t smem,
+                              const long long *off3, const int *caps, cudaStream_t s);
+template <int KIND>
+cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopParams *dprm, int n_problems, const Model *start,
+                           const int *idx, const int *off, Model *out, double *info, cudaStream_t s);
+
+struct LoopAlloc {
+    DevBuf st, wk, rngA, rngB, models, hyps, inl_best, inl_cur, flat, sample, misc, off3, caps, prm, out_models, out_stats;
+    PinBuf h_off3, h_caps, h_prm, h_active, h_out;
+};
+
+} // namespace mp

@@ -3,110 +3,36 @@
 // device functions; these entry points exist for mp_score_batch / mp_inliers and
 // the roofline measurement.
 #pragma once
-#include "mp_score.cuh"
-#include "mp_stage.cuh"
+#include "mp_block.cuh"
 
 namespace mp {
 
-// Host-filled description of one pair's raw input (already resident in HBM).
-struct PairRaw {
-    int n, kind;
-    long long off;   // match offset into the packed raw arrays (x: 2*off)
-    long long off32; // float4 offset of the fp32 staging block (multiple of 1)
-    double K0[9], K1[9], pp0[2], pp1[2], min_depth[2];
-    double thr[2], w[2]; // options.squared_inlier_thresholds / data_type_weights as given
-};
-
-// deterministic block sum (fixed tree), result valid on all threads
-__device__ __forceinline__ double block_sum(double v, double *red /*[32]*/) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-    __syncthreads();
-    if (lane == 0) red[wid] = v;
-    __syncthreads();
-    double s = 0;
-    for (int i = 0; i < nw; i++) s += red[i];
-    return s;
-}
-
-// Front-end of the three estimators on the device: principal-point subtraction and
-// poselib::normalize_points-style isotropic scaling for the focal kinds
-// (...shared_focal_estimator.cpp:14-25), the "three data types" option rewrite
-// (hybrid_pose_estimator.cpp:16-23), K^-1 and sampson_loss_scale
-// (hybrid_pose_estimator.h:21,35-36), the fp64 match records and the fp32 staging block.
+// Front-end of the three estimators on the device (math in mp_frontend.cuh): one CTA per pair.
 __global__ void __launch_bounds__(256) prep_pairs_kernel(const PairRaw *raw, const double *X0, const double *X1,
                                                          const double *D0, const double *D1, PairConst *pcs,
                                                          Match64 *M, float4 *S32) {
     __shared__ double red[32];
     const PairRaw &r = raw[blockIdx.x];
-    PairConst &pc = pcs[blockIdx.x];
-    const int n = r.n, kind = r.kind;
+    const int n = r.n;
     const double *x0 = X0 + 2 * r.off, *x1 = X1 + 2 * r.off, *d0 = D0 + r.off, *d1 = D1 + r.off;
     Match64 *m = M + r.off;
     float4 *P = S32 + r.off32, *Q = P + n;
     double ns = 1.0, K0i[9], K1i[9];
-    if (kind != CALIB) {
+    if (r.kind != CALIB) {
         double acc = 0;
-        for (int i = threadIdx.x; i < n; i += blockDim.x) {
-            double ax = x0[2 * i] - r.pp0[0], ay = x0[2 * i + 1] - r.pp0[1];
-            double bx = x1[2 * i] - r.pp1[0], by = x1[2 * i + 1] - r.pp1[1];
-            acc += sqrt(ax * ax + ay * ay) + sqrt(bx * bx + by * by);
-        }
+        for (int i = threadIdx.x; i < n; i += blockDim.x) acc += norm_scale_term(r, x0 + 2 * i, x1 + 2 * i);
         ns = block_sum(acc, red) / (sqrt(2.0) * n);
     } else {
         inv3(r.K0, K0i);
         inv3(r.K1, K1i);
     }
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        Match64 o;
-        o.d0 = d0[i]; o.d1 = d1[i];
-        float4 p, q;
-        if (kind == CALIB) {
-            o.x0x = x0[2 * i]; o.x0y = x0[2 * i + 1]; o.x1x = x1[2 * i]; o.x1y = x1[2 * i + 1];
-            double a[3], b[3];
-            mat3_vec(K0i, o.x0x, o.x0y, 1.0, a);
-            mat3_vec(K1i, o.x1x, o.x1y, 1.0, b);
-            p = make_float4((float)a[0], (float)a[1], (float)b[0], (float)b[1]);
-            q = make_float4((float)o.d0, (float)o.d1, (float)(1.0 / sqrt(a[0] * a[0] + a[1] * a[1] + 1.0)),
-                            (float)(1.0 / sqrt(b[0] * b[0] + b[1] * b[1] + 1.0)));
-        } else {
-            o.x0x = (x0[2 * i] - r.pp0[0]) / ns; o.x0y = (x0[2 * i + 1] - r.pp0[1]) / ns;
-            o.x1x = (x1[2 * i] - r.pp1[0]) / ns; o.x1y = (x1[2 * i + 1] - r.pp1[1]) / ns;
-            p = make_float4((float)o.x0x, (float)o.x0y, (float)o.x1x, (float)o.x1y);
-            q = make_float4((float)o.d0, (float)o.d1, 0.f, 0.f);
-        }
-        m[i] = o; P[i] = p; Q[i] = q;
+        float p[4], q[4];
+        prep_match(r, ns, K0i, K1i, x0 + 2 * i, x1 + 2 * i, d0[i], d1[i], &m[i], p, q);
+        P[i] = make_float4(p[0], p[1], p[2], p[3]);
+        Q[i] = make_float4(q[0], q[1], q[2], q[3]);
     }
-    if (threadIdx.x == 0) {
-        pc.n = n; pc.kind = kind; pc.off = r.off; pc.off32 = r.off32;
-        const double eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-        for (int i = 0; i < 9; i++) {
-            pc.K0[i] = kind == CALIB ? r.K0[i] : eye[i]; pc.K1[i] = kind == CALIB ? r.K1[i] : eye[i];
-            pc.K0i[i] = kind == CALIB ? K0i[i] : eye[i]; pc.K1i[i] = kind == CALIB ? K1i[i] : eye[i];
-        }
-        double tr = r.thr[0], te = r.thr[1];
-        if (kind != CALIB) { tr /= ns * ns; te /= ns * ns; }
-        double ws = r.w[1] * (2 * tr / te);
-        pc.sampson_w = ws;
-        pc.w[0] = r.w[0]; pc.w[1] = r.w[0]; pc.w[2] = ws;
-        pc.thr[0] = tr; pc.thr[1] = tr; pc.thr[2] = te;
-        pc.loss_scale = 1.0;
-        if (kind == CALIB) {
-            double l = 1.0 / (r.K0[0] + r.K0[4]) + 1.0 / (r.K1[0] + r.K1[4]);
-            pc.loss_scale = 1.0 / (l * l);
-        }
-        pc.norm_scale = ns;
-        for (int k = 0; k < 2; k++) { pc.min_depth[k] = r.min_depth[k]; pc.pp0[k] = r.pp0[k]; pc.pp1[k] = r.pp1[k]; }
-    }
-}
-
-__device__ __forceinline__ PairF make_pairf(const PairConst &pc, int score_type) {
-    PairF f;
-    f.k0fx = (float)pc.K0[0]; f.k0sk = (float)pc.K0[1]; f.k0fy = (float)pc.K0[4];
-    f.k1fx = (float)pc.K1[0]; f.k1sk = (float)pc.K1[1]; f.k1fy = (float)pc.K1[4];
-    f.thr0 = (float)pc.thr[0]; f.thr1 = (float)pc.thr[1]; f.thr2 = (float)pc.thr[2];
-    f.loss = (float)pc.loss_scale; f.n = pc.n; f.gate = score_type;
-    return f;
+    if (threadIdx.x == 0) prep_constants(r, ns, &pcs[blockIdx.x]);
 }
 
 // fp64 models -> fp32 hypothesis parameter blocks

@@ -1,0 +1,153 @@
+// K6 -- the hybrid LO-MSAC control loop on the device (hybrid_ransac.h:38-206) for a
+// batch of pairs.  The reference's loop is sequential per pair; here every ROUND runs,
+// for all pairs still iterating,
+//   sample_kernel   : solver selection + minimal samples of the next <= B iterations
+//                     (exact std::mt19937 streams, mp_rng.cuh)
+//   minimal_kernel  : one thread per sample -> <= 15 fp64 models (K1/K2)
+//   score_kernel    : fused fp32 truncated-MSAC scores of all new hypotheses (K3)
+//   decide_kernel   : one CTA per pair replays the iterations IN ORDER on the scores:
+//                     candidate bests are re-scored in fp64, best model / inliers /
+//                     per-solver iteration caps updated, local optimisation (K5) run
+//                     where the reference runs it, the break test taken per iteration.
+// Iterations after an LO event inside a batch are discarded and their random numbers
+// rewound (LO consumes stream B), so the sequence of (solver, sample) the device sees is
+// the one the sequential CPU loop sees.  Termination is decided on the device; the host
+// only relaunches rounds while the device-side count of unfinished pairs is non-zero.
+#pragma once
+#include "mp_block.cuh"
+#include "mp_lm.cuh"
+#include "mp_minimal.cuh"
+#include "mp_rng.cuh"
+
+namespace mp {
+
+constexpr int LP_BMAX = 32;            // iterations per pair per round (upper bound)
+constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
+constexpr int LP_THREADS = 256;        // decide_kernel CTA
+enum { PH_ITER = 0, PH_LO_PRE = 1, PH_LO_MAIN = 2, PH_FINISH = 3, PH_DONE = 4 };
+
+struct LoopParams {
+    mp_options opt;
+    mp_config cfg;
+    int n_pairs, bmax;
+    double guard; // relative guard band of the fp32 score filter
+};
+
+struct PairState {
+    int phase, pre_done, B, batch_len;
+    unsigned it;             // iterations completed = index of the next iteration
+    unsigned iters[2], cap[2];
+    unsigned total;          // num_iterations_total at loop exit
+    int broke;
+    double prior[2];
+    double best_min_score, best_score;
+    Model best_min, best;
+    int best_solver, ev_solver;
+    int number_lo, best_num_inliers, num_inl[3];
+    double ratios[3];
+    unsigned long long hyps_scored, evals;
+    unsigned lm_solves, lm_iters;
+    int sizes[2][3], non_min_sample_size, min_sample_size;
+};
+
+// per-pair work buffers of one round
+struct PairWork {
+    int solver[LP_BMAX];
+    int idx[LP_BMAX][8];
+    unsigned long long posA[LP_BMAX], posB[LP_BMAX]; // stream positions AFTER iteration b
+    int count[LP_BMAX];
+    float s32[LP_BMAX * LP_MM];
+};
+
+struct LoopBuffers {
+    const PairConst *pc;
+    const Match64 *M;
+    const float4 *S32;
+    PairState *st;
+    PairWork *wk;
+    MtStream *rngA, *rngB;
+    Model *models;  // [pair][LP_BMAX * LP_MM]
+    HypF *hyps;     // same indexing
+    int *inl_best;  // [3 * off] inlier lists of the global best (the caller's output layout)
+    int *inl_cur;   // [3 * off] scratch: inliers of the model being refined
+    int *flat;      // [3 * off + pad] scratch: flattened inlier list / shuffled sample
+    int *sample;    // [3 * off + pad] scratch: un-flattened sample lists
+    int *n_active;  // device counter of pairs not yet PH_DONE
+};
+
+// ---------------------------------------------------------------- block-level helpers
+// (blockDim.x <= 512, all threads participate)
+
+// exact ScoreModel (hybrid_ransac.h:265-282) of one model by the whole CTA
+__device__ __forceinline__ double block_score64(const PairConst &pc, const Match64 *m, const Model &model,
+                                                int score_type, double *red) {
+    Eval64 e;
+    make_eval64(pc, model, &e);
+    double acc = 0;
+    for (int i = threadIdx.x; i < pc.n; i += blockDim.x) {
+        const Match64 mm = m[i];
+        const double r0 = score_type == 1 ? DBL_MAX : eval64(e, mm, 0);
+        const double r1 = score_type == 1 ? DBL_MAX : eval64(e, mm, 1);
+        const double r2 = score_type == 2 ? DBL_MAX : eval64(e, mm, 2);
+        acc += pc.w[0] * msac64(r0, pc.thr[0]) + pc.w[1] * msac64(r1, pc.thr[1]) + pc.w[2] * msac64(r2, pc.thr[2]);
+    }
+    return block_sum(acc, red);
+}
+
+// GetInliers (hybrid_ransac.h:289-349): three ascending index lists, out_idx[t * n + k];
+// counts written to cnt_sh[3] (shared).  wcnt: shared int[3][16].
+__device__ __forceinline__ void block_inliers(const PairConst &pc, const Match64 *m, const Model &model,
+                                              const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16]) {
+    Eval64 e;
+    make_eval64(pc, model, &e);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    __syncthreads();
+    if (threadIdx.x < 3) cnt_sh[threadIdx.x] = 0;
+    __syncthreads();
+    for (int start = 0; start < pc.n; start += blockDim.x) {
+        const int i = start + threadIdx.x;
+        bool in[3] = {false, false, false};
+        if (i < pc.n) {
+            const Match64 mm = m[i];
+            for (int t = 0; t < 3; t++) in[t] = eval64(e, mm, t) < thr3[t];
+        }
+        unsigned bal[3];
+        for (int t = 0; t < 3; t++) {
+            bal[t] = __ballot_sync(0xffffffffu, in[t]);
+            if (lane == 0) wcnt[t][warp] = __popc(bal[t]);
+        }
+        __syncthreads();
+        for (int t = 0; t < 3; t++) {
+            int off = cnt_sh[t];
+            for (int w = 0; w < warp; w++) off += wcnt[t][w];
+            if (in[t]) out_idx[t * pc.n + off + __popc(bal[t] & ((1u << lane) - 1u))] = i;
+        }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            int s = 0;
+            for (int w = 0; w < nw; w++) s += wcnt[threadIdx.x][w];
+            cnt_sh[threadIdx.x] += s;
+        }
+        __syncthreads();
+    }
+}
+
+// utils::NumRequiredIterations (ext/RansacLib/RansacLib/utils.h:142-178), vector form
+MP_HD unsigned num_required_iterations(const double *ratios, double prob_missing, const int *sizes, unsigned mn,
+                                       unsigned mx) {
+    double p = 1.0;
+    for (int i = 0; i < 3; i++) p *= pow(ratios[i], (double)sizes[i]);
+    if (p <= 0.0) return mx;
+    if (p >= 1.0) return mn;
+    const double q = 1.0 - p;
+    if (q >= 0.99999999999999) return mx;
+    const double it = ceil(log(prob_missing) / log(q) + 0.5);
+    // the reference's static_cast<uint32_t>(double) is out of range for it >= 2^32; x86-64 gcc
+    // truncates to 64 bits and keeps the low word -- reproduced so that caps agree with the CPU loop
+    unsigned r = (unsigned)(unsigned long long)(long long)it;
+    r = r < mx ? r : mx;
+    return r > mn ? r : mn;
+}
+
+} // namespace mp
+#include "mp_loop_lo.cuh"

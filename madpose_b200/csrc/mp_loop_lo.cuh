@@ -1,0 +1,256 @@
+// LocalOptimization / LeastSquaresFit (hybrid_ransac.h:383-538) and the LM solves they
+// issue, executed by one CTA.  Control flow is uniform over the CTA: every thread runs the
+// scalar driver on identical data; the residual-block sums, inlier extraction, scoring and
+// the tail of the Fisher-Yates shuffles are spread over the threads.
+#pragma once
+
+namespace mp {
+
+struct BlockScratch { // shared memory of the decide kernel
+    double red[32];
+    double part[LP_THREADS / 32][LM_ACC_DOUBLES];
+    double total[LM_ACC_DOUBLES];
+    int cnt[3], wcnt[3][16];
+    int flag[4], base_len, fit_len, fit_cnt[3];
+    Model m_lo, m_init, m_tmp;
+};
+
+struct BlockCtx {
+    const PairConst *pc;
+    const Match64 *M;      // this pair's records
+    const LoopParams *prm;
+    PairState *S;          // shared-memory copy of the pair state
+    MtStream *rngB;
+    int *inl_cur, *flat, *base, *sample; // global scratch of this pair
+    int cap;               // capacity of flat / base and of each of the 3 sample lists
+    BlockScratch *sh;
+};
+
+// ---- collective evaluation of cost, J^T J, J^T r
+template <int KIND> struct BlockEval {
+    const BlockCtx *C;
+    const LmSetup *L;
+    const int *lst[3];
+    int n[3];
+    __device__ void operator()(const double *x, LmAcc *out) const {
+        LmPoint p;
+        lm_point(KIND, x, &p);
+        LmAcc a;
+        a.clear();
+        const int n0 = L->use_reproj ? n[0] : 0, n1 = L->use_reproj ? n[1] : 0, n2 = L->use_samp ? n[2] : 0;
+        const int ntot = n0 + n1 + n2;
+        for (int j = threadIdx.x; j < ntot; j += blockDim.x) {
+            int t, k;
+            if (j < n0) { t = 0; k = j; } else if (j < n0 + n1) { t = 1; k = j - n0; } else { t = 2; k = j - n0 - n1; }
+            const Match64 m = C->M[lst[t][k]];
+            lm_block<KIND>(*C->pc, m, t, p, L->W, &a);
+        }
+        BlockScratch *sh = C->sh;
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+        double *av = reinterpret_cast<double *>(&a);
+        __syncthreads();
+#pragma unroll
+        for (int v = 0; v < LM_ACC_DOUBLES; v++) {
+            double s = av[v];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0) sh->part[warp][v] = s;
+        }
+        __syncthreads();
+        if (threadIdx.x < LM_ACC_DOUBLES) {
+            double s = 0;
+            for (int w = 0; w < nw; w++) s += sh->part[w][threadIdx.x];
+            sh->total[threadIdx.x] = s;
+        }
+        __syncthreads();
+        double *ov = reinterpret_cast<double *>(out);
+        for (int v = 0; v < LM_ACC_DOUBLES; v++) ov[v] = sh->total[v];
+    }
+};
+static_assert(sizeof(LmAcc) == LM_ACC_DOUBLES * sizeof(double), "LmAcc is a flat array of doubles");
+
+// NonMinimalSolver / LeastSquares on explicit lists; *m is a shared-memory model.
+template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, int n0, const int *l1, int n1,
+                                              const int *l2, int n2, Model *m) {
+    LmSetup L;
+    if (!lm_setup(*C.pc, C.prm->cfg, n0, n1, n2, &L)) return;
+    BlockEval<KIND> ev;
+    ev.C = &C; ev.L = &L; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
+    double x[LM_NA];
+    LmInfo info;
+    __syncthreads();
+    lm_model_to_x(*m, x);
+    lm_minimize(L, ev, x, &info);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        lm_x_to_model(KIND, x, m);
+        C.S->lm_solves += 1; C.S->lm_iters += info.iterations;
+    }
+    __syncthreads();
+}
+
+// utils::RandomShuffleAndResize (ext/RansacLib/RansacLib/utils.h:48-73) on v[0..*len) with
+// stream B.  Positions < target are final after `target` swap steps; the remaining steps
+// only consume random words, which the CTA checks in parallel for Lemire rejections.
+__device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *v, int *len_sh) {
+    MtStream *g = C.rngB;
+    __syncthreads();
+    const int n = *len_sh;
+    __syncthreads();
+    const int head = n - 1 < target ? (n - 1 > 0 ? n - 1 : 0) : target;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < head; i++) {
+            const int j = mt_uniform_int(g, i, n - 1);
+            const int t = v[i]; v[i] = v[j]; v[j] = t;
+        }
+    }
+    __syncthreads();
+    int i = head; // remaining draws: uniform_int(i, n-1) for i in [head, n-1)
+    while (i < n - 1) {
+        if (g->pos == g->gen) mt_refill(g, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
+        const unsigned long long pos = g->pos;
+        const int avail = (int)(g->gen - pos), m = avail < n - 1 - i ? avail : n - 1 - i;
+        int first = m;
+        for (int j = threadIdx.x; j < m; j += blockDim.x) {
+            const uint32_t w = mt_temper(g->x[(pos + j) % MT_RING]);
+            if (mt_lemire_rejects(w, (uint32_t)(n - (i + j)))) { first = j; break; }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) C.sh->flag[0] = m;
+        __syncthreads();
+        if (first < m) atomicMin(&C.sh->flag[0], first);
+        __syncthreads();
+        first = C.sh->flag[0];
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            g->pos = pos + first;
+            if (first < m) (void)mt_uniform_int(g, i + first, n - 1); // the draw with a rejection, sequentially
+        }
+        i += first + (first < m ? 1 : 0);
+        __syncthreads();
+    }
+    // resize: shrink, or grow with zeros (quirk Q3)
+    for (int k = n + threadIdx.x; k < target; k += blockDim.x) v[k] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) *len_sh = target;
+    __syncthreads();
+}
+
+// un-flatten (hybrid_ransac.h:443-449, 528-534): entry e -> (type e / n, index e % n), order kept
+__device__ inline void block_unflatten(const BlockCtx &C, const int *flat, int len, int *cnt3_sh) {
+    const int n = C.pc->n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int c[3] = {0, 0, 0};
+        for (int k = 0; k < len; k++) {
+            int e = flat[k], t = 0;
+            while (e >= n && t < 2) { e -= n; t++; }
+            C.sample[t * C.cap + c[t]++] = e;
+        }
+        cnt3_sh[0] = c[0]; cnt3_sh[1] = c[1]; cnt3_sh[2] = c[2];
+    }
+    __syncthreads();
+}
+
+// LeastSquaresFit (hybrid_ransac.h:484-538)
+template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const double *thr, int solver, Model *m,
+                                                  bool all_inliers) {
+    BlockScratch *sh = C.sh;
+    const int n = C.pc->n;
+    block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt);
+    const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
+    const int *sz = C.S->sizes[solver];
+    if (c0 < sz[0] || c1 < sz[1] || c2 < sz[2]) return;
+    if (all_inliers) {
+        block_lsq<KIND>(C, C.inl_cur, c0, C.inl_cur + n, c1, C.inl_cur + 2 * n, c2, m);
+        return;
+    }
+    const int mult = C.prm->opt.min_sample_multiplicator;
+    const int k0 = min(sz[0] * mult, c0), k1 = min(sz[1] * mult, c1), k2 = min(sz[2] * mult, c2);
+    const int total = (k0 + k1 + k2) * mult; // x7 applied twice (quirk Q4)
+    for (int k = threadIdx.x; k < c0; k += blockDim.x) C.flat[k] = C.inl_cur[k];
+    for (int k = threadIdx.x; k < c1; k += blockDim.x) C.flat[c0 + k] = C.inl_cur[n + k] + n;
+    for (int k = threadIdx.x; k < c2; k += blockDim.x) C.flat[c0 + c1 + k] = C.inl_cur[2 * n + k] + 2 * n;
+    __syncthreads();
+    if (threadIdx.x == 0) sh->fit_len = c0 + c1 + c2;
+    block_shuffle_resize(C, total, C.flat, &sh->fit_len);
+    block_unflatten(C, C.flat, total, sh->fit_cnt);
+    const int s0 = sh->fit_cnt[0], s1 = sh->fit_cnt[1], s2 = sh->fit_cnt[2];
+    block_lsq<KIND>(C, C.sample, s0, C.sample + C.cap, s1, C.sample + 2 * C.cap, s2, m);
+}
+
+// ScoreModel in fp64 + the work counters of the loop
+__device__ inline double block_score_counted(const BlockCtx &C, const Model &m) {
+    const double s = block_score64(*C.pc, C.M, m, C.prm->cfg.score_type, C.sh->red);
+    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; }
+    return s;
+}
+
+// LocalOptimization (hybrid_ransac.h:383-482).  best / best_score / best_solver live in shared memory.
+template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, int solver, Model *best,
+                                                             double *best_score, int *best_solver) {
+    BlockScratch *sh = C.sh;
+    const PairConst &pc = *C.pc;
+    const mp_options &o = C.prm->opt;
+    const int n = pc.n;
+    double thr[3], step[3];
+    for (int t = 0; t < 3; t++) {
+        step[t] = (o.threshold_multiplier - 1.0) * pc.thr[t] / (double)(o.num_lsq_iterations - 1);
+        thr[t] = pc.thr[t] * o.threshold_multiplier;
+    }
+    auto update_best = [&](double sc, const Model *m) {
+        __syncthreads();
+        if (threadIdx.x == 0 && sc < *best_score) { *best_score = sc; *best = *m; *best_solver = solver; }
+        __syncthreads();
+    };
+    __syncthreads();
+    if (threadIdx.x == 0) sh->m_init = *best;
+    __syncthreads();
+    block_lsq_fit<KIND>(C, thr, solver, &sh->m_init, true);
+    double sc = block_score_counted(C, sh->m_init);
+    update_best(sc, &sh->m_init);
+    // base inliers of m_init at the nominal thresholds, flattened with type offsets
+    block_inliers(pc, C.M, sh->m_init, pc.thr, C.inl_cur, sh->cnt, sh->wcnt);
+    const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
+    for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
+    for (int k = threadIdx.x; k < c1; k += blockDim.x) C.base[c0 + k] = C.inl_cur[n + k] + n;
+    for (int k = threadIdx.x; k < c2; k += blockDim.x) C.base[c0 + c1 + k] = C.inl_cur[2 * n + k] + 2 * n;
+    __syncthreads();
+    if (threadIdx.x == 0) sh->base_len = c0 + c1 + c2; // current length of the base list
+    __syncthreads();
+    const int nonmin = max(C.S->non_min_sample_size, min(C.S->min_sample_size * o.non_min_sample_multiplier, (c0 + c1 + c2) / 2));
+    for (int r = 0; r < o.num_lo_steps; ++r) {
+        // the sample is the list BEFORE this step's shuffle (quirk Q2)
+        // (step 0: all base inliers = the three lists still held in inl_cur; later steps: the
+        // nonmin-element list left by the previous shuffle)
+        const int blen = sh->base_len;
+        int s0 = c0, s1 = c1, s2 = c2;
+        const int *l0 = C.inl_cur, *l1 = C.inl_cur + n, *l2 = C.inl_cur + 2 * n;
+        __syncthreads();
+        if (r > 0) {
+            block_unflatten(C, C.base, blen, sh->fit_cnt);
+            s0 = sh->fit_cnt[0]; s1 = sh->fit_cnt[1]; s2 = sh->fit_cnt[2];
+            l0 = C.sample; l1 = C.sample + C.cap; l2 = C.sample + 2 * C.cap;
+        }
+        __syncthreads();
+        block_shuffle_resize(C, nonmin, C.base, &sh->base_len);
+        LmSetup Lg;
+        if (!lm_setup(pc, C.prm->cfg, s0, s1, s2, &Lg)) continue; // NonMinimalSolver returned 0
+        if (threadIdx.x == 0) sh->m_lo = sh->m_init;
+        __syncthreads();
+        block_lsq<KIND>(C, l0, s0, l1, s1, l2, s2, &sh->m_lo);
+        sc = block_score_counted(C, sh->m_lo);
+        update_best(sc, &sh->m_lo);
+        block_lsq_fit<KIND>(C, pc.thr, solver, &sh->m_lo, false);
+        double cur[3] = {thr[0], thr[1], thr[2]};
+        for (int i = 0; i < o.num_lsq_iterations; ++i) {
+            block_lsq_fit<KIND>(C, cur, solver, &sh->m_lo, false);
+            sc = block_score_counted(C, sh->m_lo);
+            update_best(sc, &sh->m_lo);
+            for (int t = 0; t < 3; t++) cur[t] -= step[t];
+        }
+    }
+    __syncthreads();
+}
+
+} // namespace mp

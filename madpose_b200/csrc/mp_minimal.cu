@@ -1,0 +1,88 @@
+// K1/K2 translation unit: the per-sample fp64 minimal solvers (compiled once, shared by the
+// stand-alone entry point and the loop's batch kernel) and mp_minimal_solve_batch.
+#include "mp_host.cuh"
+#include "mp_loop.cuh"
+#include "mp_minimal.cuh"
+
+namespace mp {
+
+__device__ __noinline__ int minimal_solver_ni(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx,
+                                              bool min_depth_on, Model *out) {
+    return minimal_solver(pc, M, solver_idx, idx, min_depth_on, out);
+}
+
+// K1/K2 stand-alone: one thread per sample of one pair (mp_minimal_solve_batch)
+__global__ void __launch_bounds__(64) minimal_kernel(const PairConst *pcp, const Match64 *M, int solver_idx, int k,
+                                                     int n_samples, const int *idx, int min_depth_on, int max_models,
+                                                     Model *out, int *counts) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_samples) return;
+    const PairConst &pc = *pcp;
+    Model tmp[kMaxModelsAny];
+    int c = minimal_solver_ni(pc, M + pc.off, solver_idx, idx + (size_t)s * k, min_depth_on != 0, tmp);
+    if (c > max_models) c = max_models;
+    counts[s] = c;
+    for (int j = 0; j < c; j++) out[(size_t)s * max_models + j] = tmp[j];
+}
+
+// ---- K1/K2 over all samples of the round: one thread per (pair, iteration)
+__global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp) {
+    const LoopParams &prm = *prmp;
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = g / LP_BMAX, b = g % LP_BMAX;
+    if (p >= prm.n_pairs) return;
+    const PairState &S = L.st[p];
+    if (S.phase != PH_ITER || b >= S.batch_len) return;
+    const PairConst &pc = L.pc[p];
+    PairWork &W = L.wk[p];
+    Model tmp[LP_MM];
+    const int c = minimal_solver_ni(pc, L.M + pc.off, W.solver[b], W.idx[b], prm.cfg.min_depth_constraint != 0, tmp);
+    W.count[b] = c;
+    Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
+    HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
+    for (int j = 0; j < c; j++) { out[j] = tmp[j]; pack_hyp(pc.kind, tmp[j], hy + j); }
+}
+
+
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int n_pairs, cudaStream_t s) {
+    minimal_batch_kernel<<<(n_pairs * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm);
+    return cudaGetLastError();
+}
+
+} // namespace mp
+
+extern "C" {
+int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *pair, const mp_options *opt,
+                           const mp_config *cfg, int n_samples, const int32_t *sample_idx, mp_model *out_models,
+                           int32_t *out_counts) {
+    using namespace mp;
+    if (!c || !pair || !opt || !cfg || !sample_idx || !out_models || !out_counts || n_samples <= 0 || solver_idx < 0 ||
+        solver_idx > 1)
+        return fail(MP_ERR_ARG, "mp_minimal_solve_batch: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    int rc = upload_pairs(c, kind, 1, pair, opt);
+    if (rc) return rc;
+    const int k = solver_idx == 0 ? (kind == CALIB ? 3 : 4) : (kind == CALIB ? 5 : (kind == SHARED ? 6 : 7));
+    const int mm = solver_idx == 0 ? kMaxModelsAffine[kind] : kMaxModelsPoints[kind];
+    for (size_t i = 0; i < (size_t)n_samples * k; i++)
+        if (sample_idx[i] < 0 || sample_idx[i] >= pair->n) return fail(MP_ERR_ARG, "sample index out of range");
+    MP_CUDA(c->d_idx.reserve((size_t)n_samples * k * sizeof(int)));
+    MP_CUDA(c->d_models.reserve((size_t)n_samples * mm * sizeof(Model)));
+    MP_CUDA(c->d_misc.reserve((size_t)n_samples * sizeof(int)));
+    MP_CUDA(cudaMemcpyAsync(c->d_idx.p, sample_idx, (size_t)n_samples * k * sizeof(int), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    minimal_kernel<<<(n_samples + 63) / 64, 64, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), solver_idx, k,
+                                                        n_samples, c->d_idx.as<int>(), cfg->min_depth_constraint, mm,
+                                                        c->d_models.as<Model>(), c->d_misc.as<int>());
+    MP_CUDA(cudaGetLastError());
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    MP_CUDA(cudaMemcpyAsync(out_models, c->d_models.p, (size_t)n_samples * mm * sizeof(Model), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(out_counts, c->d_misc.p, (size_t)n_samples * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float ms = 0;
+    MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 2;
+    return MP_OK;
+}
+}

@@ -1,0 +1,159 @@
+// MinimalSolver of the three hybrid estimators on one sample, fp64, one thread:
+//   solver 0: affine-depth solver + Kabsch + min-depth filter
+//             (hybrid_pose_estimator.cpp:65-120, ...shared_focal....cpp:53-84, ...two_focal....cpp:77-113)
+//   solver 1: point-only relative pose, DLT triangulation, affine depth fits
+//             (hybrid_pose_estimator.cpp:121-187, ...shared_focal....cpp:85-130, ...two_focal....cpp:114-185)
+// Models come out in the estimator's internal units, in the solver's root order.
+#pragma once
+#include "mp_affine.cuh"
+#include "mp_relpose.cuh"
+
+namespace mp {
+
+template <int KIND> MP_HD int minimal_affine(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on,
+                                             Model *out) {
+    constexpr int NPT = KIND == CALIB ? 3 : 4;
+    double x0[NPT][3], x1[NPT][3], d0[NPT], d1[NPT];
+    for (int k = 0; k < NPT; k++) {
+        const Match64 m = M[idx[k]];
+        if (KIND == CALIB) { mat3_vec(pc.K0i, m.x0x, m.x0y, 1.0, x0[k]); mat3_vec(pc.K1i, m.x1x, m.x1y, 1.0, x1[k]); }
+        else { x0[k][0] = m.x0x; x0[k][1] = m.x0y; x0[k][2] = 1.0; x1[k][0] = m.x1x; x1[k][1] = m.x1y; x1[k][2] = 1.0; }
+        d0[k] = m.d0; d1[k] = m.d1;
+    }
+    AffSol sols[8];
+    int ns;
+    if (KIND == CALIB) ns = affine_calibrated(x0, x1, d0, d1, sols);
+    else if (KIND == SHARED) ns = affine_shared_focal(x0, x1, d0, d1, sols);
+    else ns = affine_two_focal(x0, x1, d0, d1, sols);
+    int n = 0;
+    for (int q = 0; q < ns; q++) {
+        const AffSol &s = sols[q];
+        double X[NPT][3], Y[NPT][3];
+        bool pos = true;
+        const double fa = KIND == CALIB ? 1.0 : s.f1, fb = KIND == CALIB ? 1.0 : s.f2;
+        for (int k = 0; k < NPT; k++) {
+            const double e1 = d0[k] + s.b1, e2 = d1[k] * s.a2 + s.b2 * s.a2;
+            if (e1 <= 0 || e2 <= 0) pos = false; // solver.cpp:503,702,1006
+            X[k][0] = x0[k][0] / fa * e1; X[k][1] = x0[k][1] / fa * e1; X[k][2] = x0[k][2] * e1;
+            Y[k][0] = x1[k][0] / fb * e2; Y[k][1] = x1[k][1] / fb * e2; Y[k][2] = x1[k][2] * e2;
+        }
+        if (!pos) continue;
+        Model m;
+        if (!kabsch<NPT>(X, Y, m.R, m.t)) continue;
+        m.scale = s.a2; m.o0 = s.b1; m.o1 = s.b2 * s.a2; m.f0 = fa; m.f1 = fb;
+        if (min_depth_on && !(m.o0 > -pc.min_depth[0] && m.o1 > -pc.min_depth[1] * m.scale)) continue;
+        m.o1 /= m.scale;
+        if (model_finite(m)) out[n++] = m;
+    }
+    return n;
+}
+
+// triangulate the sample with K0 [I|0], K1 [R|t]; fit prior depth -> triangulated depth
+// affinely in both views (hybrid_pose_estimator.cpp:137-182)
+template <int NPT> MP_HD bool depth_fit_tail(const PairConst &pc, const double *d0s, const double *d1s,
+                                             const double (*p0)[2], const double (*p1)[2], double f0, double f1,
+                                             bool min_depth_on, Model *m) {
+    const double P0[12] = {f0, 0, 0, 0, 0, f0, 0, 0, 0, 0, 1, 0};
+    double P1[12];
+    for (int i = 0; i < 3; i++) {
+        const double k = i < 2 ? f1 : 1.0;
+        for (int j = 0; j < 3; j++) P1[4 * i + j] = k * m->R[3 * i + j];
+        P1[4 * i + 3] = k * m->t[i];
+    }
+    double X[NPT][3], z[NPT];
+    for (int k = 0; k < NPT; k++) {
+        double Q[4];
+        triangulate_h(P0, P1, p0[k], p1[k], Q);
+        for (int c = 0; c < 3; c++) X[k][c] = Q[c] / Q[3];
+        z[k] = X[k][2];
+    }
+    double s0, c0;
+    fit_affine(NPT, d0s, z, &s0, &c0);
+    const double off0 = c0 / s0;
+    if (min_depth_on && off0 < -pc.min_depth[0]) return false;
+    for (int k = 0; k < 3; k++) m->t[k] /= s0;
+    for (int k = 0; k < NPT; k++) {
+        const double Xs[3] = {X[k][0] / s0, X[k][1] / s0, X[k][2] / s0};
+        double Y[3];
+        mat3_vecp(m->R, Xs, Y);
+        z[k] = Y[2] + m->t[2];
+    }
+    double s1, c1;
+    fit_affine(NPT, d1s, z, &s1, &c1);
+    const double off1 = c1 / s1;
+    if (min_depth_on && off1 < -pc.min_depth[1]) return false;
+    m->scale = s1; m->o0 = off0; m->o1 = off1;
+    return model_finite(*m);
+}
+
+template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on,
+                                             Model *out) {
+    constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
+    double b0[NPT][3], b1[NPT][3], p0[NPT][2], p1[NPT][2], d0[NPT], d1[NPT];
+    for (int k = 0; k < NPT; k++) {
+        const Match64 m = M[idx[k]];
+        double a[3], b[3];
+        if (KIND == CALIB) { mat3_vec(pc.K0i, m.x0x, m.x0y, 1.0, a); mat3_vec(pc.K1i, m.x1x, m.x1y, 1.0, b); }
+        else { a[0] = m.x0x; a[1] = m.x0y; a[2] = 1.0; b[0] = m.x1x; b[1] = m.x1y; b[2] = 1.0; }
+        const double na = norm3(a), nb = norm3(b);
+        for (int c = 0; c < 3; c++) { b0[k][c] = a[c] / na; b1[k][c] = b[c] / nb; }
+        p0[k][0] = a[0]; p0[k][1] = a[1]; p1[k][0] = b[0]; p1[k][1] = b[1];
+        d0[k] = m.d0; d1[k] = m.d1;
+    }
+    int n = 0;
+    if (KIND == CALIB) {
+        Pose poses[10];
+        const int np = relpose_5pt(b0, b1, poses);
+        for (int q = 0; q < np; q++) {
+            Model m;
+            for (int k = 0; k < 9; k++) m.R[k] = poses[q].R[k];
+            for (int k = 0; k < 3; k++) m.t[k] = poses[q].t[k];
+            m.f0 = 1.0; m.f1 = 1.0;
+            if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, 1.0, 1.0, min_depth_on, &m)) out[n++] = m;
+        }
+    } else if (KIND == SHARED) {
+        double h0[NPT][3], h1[NPT][3];
+        for (int k = 0; k < NPT; k++) { h0[k][0] = p0[k][0]; h0[k][1] = p0[k][1]; h0[k][2] = 1; h1[k][0] = p1[k][0]; h1[k][1] = p1[k][1]; h1[k][2] = 1; }
+        FocalPose fps[15];
+        const int np = relpose_6pt_shared_focal(h0, h1, fps);
+        for (int q = 0; q < np; q++) {
+            Model m;
+            for (int k = 0; k < 9; k++) m.R[k] = fps[q].pose.R[k];
+            for (int k = 0; k < 3; k++) m.t[k] = fps[q].pose.t[k];
+            m.f0 = fps[q].focal; m.f1 = fps[q].focal;
+            if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, m.f0, m.f1, min_depth_on, &m)) out[n++] = m;
+        }
+    } else {
+        double Fs[3][9];
+        const int nf = fundamental_7pt(b0, b1, Fs);
+        for (int q = 0; q < nf; q++) {
+            double f0sq, f1sq;
+            bougnoux_focals(Fs[q], &f0sq, &f1sq);
+            const double f0 = sqrt(fabs(f0sq)), f1 = sqrt(fabs(f1sq)); // ...two_focal....cpp:121-122
+            if (!finite_d(f0) || !finite_d(f1) || f0 == 0.0 || f1 == 0.0) continue;
+            double E[9]; // E = K1^T F K0
+            for (int i = 0; i < 3; i++)
+                for (int j = 0; j < 3; j++) E[3 * i + j] = Fs[q][3 * i + j] * (i < 2 ? f1 : 1.0) * (j < 2 ? f0 : 1.0);
+            Model m;
+            recover_pose<NPT>(E, p0, p1, 1e9, m.R, m.t); // un-calibrated points with K = I, as the reference does
+            m.f0 = f0; m.f1 = f1;
+            if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, f0, f1, min_depth_on, &m)) out[n++] = m;
+        }
+    }
+    return n;
+}
+
+// dispatch; out must hold kMaxModelsAny models
+MP_HD int minimal_solver(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx, bool min_depth_on,
+                         Model *out) {
+    if (solver_idx == 0) {
+        if (pc.kind == CALIB) return minimal_affine<CALIB>(pc, M, idx, min_depth_on, out);
+        if (pc.kind == SHARED) return minimal_affine<SHARED>(pc, M, idx, min_depth_on, out);
+        return minimal_affine<TWO>(pc, M, idx, min_depth_on, out);
+    }
+    if (pc.kind == CALIB) return minimal_points<CALIB>(pc, M, idx, min_depth_on, out);
+    if (pc.kind == SHARED) return minimal_points<SHARED>(pc, M, idx, min_depth_on, out);
+    return minimal_points<TWO>(pc, M, idx, min_depth_on, out);
+}
+
+} // namespace mp

@@ -1,0 +1,118 @@
+// std::mt19937 + the libstdc++ distributions the reference's control loop draws from,
+// reproduced on the device so that the GPU loop consumes exactly the random streams of
+// the CPU loop: stream A = HybridUniformSampling::rng_
+// (ext/RansacLib/RansacLib/hybrid_sampling.h:52,134), stream B = the loop's own engine
+// (hybrid_ransac.h:79-80: solver selection and every LO shuffle).
+// The generator state IS a ring of raw (untempered) words: word r >= 624 is
+// x[r] = x[r-227] ^ twist(x[r-624], x[r-623]); keeping the last MT_RING raw words lets the
+// loop rewind a stream by up to MT_RING-624 outputs (speculative batches of iterations).
+#pragma once
+#include "mp_common.cuh"
+
+namespace mp {
+
+constexpr int MT_N = 624, MT_M = 397, MT_RING = 4 * MT_N;
+
+struct MtStream {
+    uint32_t x[MT_RING];
+    unsigned long long gen; // raw words generated so far (multiple of 624, >= 624)
+    unsigned long long pos; // raw index of the next output word (>= 624)
+};
+
+// seeds raw words 0..623 (std::mersenne_twister_engine::seed)
+MP_HD void mt_seed(MtStream *s, uint32_t seed) {
+    s->x[0] = seed;
+    for (int i = 1; i < MT_N; i++) s->x[i] = 1812433253u * (s->x[i - 1] ^ (s->x[i - 1] >> 30)) + (uint32_t)i;
+    s->gen = MT_N; s->pos = MT_N;
+}
+MP_HD uint32_t mt_twist(uint32_t a, uint32_t b, uint32_t c) {
+    const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+    return c ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+}
+MP_HD uint32_t mt_temper(uint32_t y) {
+    y ^= (y >> 11);
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= (y >> 18);
+    return y;
+}
+// generates raw words gen .. gen+623.  `lane`/`nlanes` spread each of the three
+// dependency-free phases over cooperating threads; SYNC separates the phases
+// (a no-op functor for a single thread).
+template <class Sync> MP_HD void mt_refill(MtStream *s, int lane, int nlanes, Sync sync) {
+    const unsigned long long g = s->gen;
+    const int bounds[4] = {0, MT_N - MT_M, 2 * (MT_N - MT_M), MT_N};
+    for (int ph = 0; ph < 3; ph++) {
+        for (int i = bounds[ph] + lane; i < bounds[ph + 1]; i += nlanes) {
+            const unsigned long long r = g + i;
+            s->x[r % MT_RING] = mt_twist(s->x[(r - MT_N) % MT_RING], s->x[(r - MT_N + 1) % MT_RING],
+                                         s->x[(r - MT_N + MT_M) % MT_RING]);
+        }
+        sync();
+    }
+    if (lane == 0) s->gen = g + MT_N;
+    sync();
+}
+struct NoSync { MP_HD void operator()() const {} };
+
+// single-thread draw
+MP_HD uint32_t mt_next(MtStream *s) {
+    if (s->pos == s->gen) mt_refill(s, 0, 1, NoSync());
+    const uint32_t y = s->x[s->pos % MT_RING];
+    s->pos++;
+    return mt_temper(y);
+}
+// std::uniform_int_distribution<int>(a, b) on a 32-bit engine (libstdc++ 13: Lemire's method)
+MP_HD int mt_uniform_int(MtStream *s, int a, int b) {
+    const uint32_t range = (uint32_t)(b - a) + 1u; // never 0 here (b - a < 2^32 - 1)
+    unsigned long long prod = (unsigned long long)mt_next(s) * range;
+    uint32_t low = (uint32_t)prod;
+    if (low < range) {
+        const uint32_t thr = (0u - range) % range;
+        while (low < thr) {
+            prod = (unsigned long long)mt_next(s) * range;
+            low = (uint32_t)prod;
+        }
+    }
+    return a + (int)(prod >> 32);
+}
+// would the word `w` be rejected by uniform_int with this range?
+MP_HD bool mt_lemire_rejects(uint32_t w, uint32_t range) {
+    const uint32_t low = (uint32_t)((unsigned long long)w * range);
+    return low < range && low < (0u - range) % range;
+}
+// std::uniform_real_distribution<double>(0, hi): generate_canonical<double, 53> = two words
+MP_HD double mt_uniform_real(MtStream *s, double hi) {
+    const double lo32 = (double)mt_next(s), hi32 = (double)mt_next(s);
+    double c = (lo32 + hi32 * 4294967296.0) / 18446744073709551616.0;
+    if (c >= 1.0) c = 1.0 - 1.1102230246251565e-16; // nextafter(1, 0)
+    return c * hi; // (b - a) * c + a with a = 0
+}
+
+// HybridUniformSampling::DrawSample / ShuffleSample for one data type (hybrid_sampling.h:84-131):
+// k distinct indices of [0, n).  scratch: n ints, only touched on the Fisher-Yates branch.
+MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
+    if (k <= 0) return;
+    const double coeff = (double)n / (double)(n - k);
+    if (coeff < 2.718281828459045235360287471352662498) {
+        for (int i = 0; i < k; i++) {
+            bool dup = true;
+            while (dup) {
+                dup = false;
+                out[i] = mt_uniform_int(s, 0, n - 1);
+                for (int j = 0; j < i; j++)
+                    if (out[j] == out[i]) { dup = true; break; }
+            }
+        }
+    } else {
+        for (int i = 0; i < n; i++) scratch[i] = i;
+        if (k != n)
+            for (int i = 0; i < n - 1; i++) {
+                const int j = mt_uniform_int(s, i, n - 1);
+                const int t = scratch[i]; scratch[i] = scratch[j]; scratch[j] = t;
+            }
+        for (int i = 0; i < k; i++) out[i] = scratch[i];
+    }
+}
+
+} // namespace mp

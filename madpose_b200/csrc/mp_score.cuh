@@ -139,4 +139,31 @@ __device__ __forceinline__ void warp_score_chunk(const TileF &tile, const PairF 
     }
 }
 
+// Same, for hypotheses addressed through an index list (the round's compacted hypotheses).
+template <int KIND>
+__device__ __forceinline__ void warp_score_list(const TileF &tile, const PairF &pf, const float w0, const float w2,
+                                                const HypF *hyps, const unsigned short *list, int cnt, int lo, int hi,
+                                                float *out /*[MP_HT]*/) {
+    const int lane = threadIdx.x & 31;
+    HypR h[MP_HT];
+#pragma unroll
+    for (int j = 0; j < MP_HT; j++) load_hyp(hyps + list[j < cnt ? j : 0], h[j]);
+    float s0[MP_HT], s1[MP_HT], s2[MP_HT];
+#pragma unroll
+    for (int j = 0; j < MP_HT; j++) { s0[j] = 0.f; s1[j] = 0.f; s2[j] = 0.f; }
+    for (int i = lo + lane; i < hi; i += 32) {
+        float4 P = tile.P[i], Q = tile.Q[i];
+#pragma unroll
+        for (int j = 0; j < MP_HT; j++) eval32<KIND>(h[j], pf, P, Q, s0[j], s1[j], s2[j]);
+    }
+    const float m = (float)(hi - lo);
+#pragma unroll
+    for (int j = 0; j < MP_HT; j++) {
+        float a = warp_sum(s0[j]), b = warp_sum(s1[j]), c = warp_sum(s2[j]);
+        if (pf.gate == 1) { a = m * pf.thr0; b = m * pf.thr1; }
+        if (pf.gate == 2) { c = m * pf.thr2; }
+        out[j] = fmaf(w0, a + b, w2 * c);
+    }
+}
+
 } // namespace mp

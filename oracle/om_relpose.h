@@ -204,6 +204,21 @@ inline int relpose_5pt_essential(const double (*x1)[3], const double (*x2)[3], s
         double d = poly_eval(m2, z);
         if (d == 0 || !std::isfinite(d)) continue;
         double x = poly_eval(m0, z) / d, y = poly_eval(m1, z) / d;
+        // Gauss-Newton polish of (x, y, z) on the ten cubic constraints: the expanded degree-10
+        // determinant only locates the root (its coefficients lose digits)
+        for (int it = 0; it < 5; it++) {
+            double JtJ[9] = {0}, Jtr[3] = {0};
+            for (int r = 0; r < 10; r++) {
+                double g[3], f = p3_eval(eq[r], x, y, z, g);
+                for (int i = 0; i < 3; i++) { Jtr[i] += g[i] * f; for (int j = 0; j < 3; j++) JtJ[3 * i + j] += g[i] * g[j]; }
+            }
+            double inv[9], st[3];
+            if (!mat3_inv(JtJ, inv)) break;
+            mat3_vec(inv, Jtr, st);
+            if (!std::isfinite(st[0] + st[1] + st[2])) break;
+            x -= st[0]; y -= st[1]; z -= st[2];
+            if (std::fabs(st[0]) <= 1e-15 * std::fabs(x) && std::fabs(st[1]) <= 1e-15 * std::fabs(y) && std::fabs(st[2]) <= 1e-15 * std::fabs(z)) break;
+        }
         std::vector<double> Ev(9);
         for (int k = 0; k < 9; k++) Ev[k] = x * N[k] + y * N[9 + k] + z * N[18 + k] + N[27 + k];
         bool ok = true;
