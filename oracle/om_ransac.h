@@ -59,7 +59,9 @@ struct Ransac {
         double q = 1.0 - p;
         if (q >= 0.99999999999999) return mx;
         double it = std::ceil(std::log(prob_missing) / std::log(q) + 0.5);
-        uint32_t r = std::min((uint32_t)it, mx);
+        // static_cast<uint32_t>(double) in the reference (RansacLib utils.h:176) is out of range for it >= 2^32;
+        // x86-64 gcc truncates to 64 bits and keeps the low word -- made explicit here
+        uint32_t r = std::min((uint32_t)(uint64_t)(int64_t)it, mx);
         return std::max(mn, r);
     }
     void update_termination(const Model &m) {

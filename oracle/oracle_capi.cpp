@@ -106,6 +106,22 @@ int om_lm(int kind, const mp_pair *pair, const mp_options *opt, const mp_config 
     return 0;
 }
 
+// utils::NumRequiredIterations restatement (KAT-1b of SURVEY.md Appendix C)
+unsigned om_num_required_iterations(const double *ratios3, double prob_missing, const int *sizes3, unsigned mn, unsigned mx) {
+    return om::Ransac::num_required_iterations(ratios3, prob_missing, sizes3, mn, mx);
+}
+// utils::RandomShuffleAndResize restatement on std::mt19937(seed): v has room for max(n, target) ints
+int om_shuffle_resize(unsigned seed, int target, int n, int *v, int second_target, int second_n, int *v2) {
+    std::mt19937 g(seed);
+    std::vector<int> a(v, v + n);
+    om::Ransac::shuffle_resize(target, &g, &a);
+    for (int i = 0; i < target; i++) v[i] = a[i];
+    std::vector<int> b(v2, v2 + second_n);
+    om::Ransac::shuffle_resize(second_target, &g, &b);
+    for (int i = 0; i < second_target; i++) v2[i] = b[i];
+    return 0;
+}
+
 static void fill_stats(const om::Stats &st, int n, mp_stats *o, int *inl) {
     std::memset(o, 0, sizeof(*o));
     o->num_iterations_total = st.num_iterations_total;

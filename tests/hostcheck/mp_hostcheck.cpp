@@ -5,6 +5,8 @@
 #include "../../madpose_b200/csrc/mp_frontend.cuh"
 #include "../../madpose_b200/csrc/mp_minimal.cuh"
 #include "../../madpose_b200/csrc/mp_lm.cuh"
+#include "../../madpose_b200/csrc/mp_rng.cuh"
+#include <random>
 #include <cstring>
 #include <vector>
 

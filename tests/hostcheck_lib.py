@@ -40,6 +40,13 @@ class HostCheck:
         return out, info
 
 
+    def rng_check(self, seed, n):
+        out = np.zeros(6, np.uint32); r0 = C.c_double()
+        self.lib.hc_rng_check(C.c_uint(seed), int(n), _ptr(out), C.byref(r0))
+        return dict(first=[int(out[0]), int(out[1])], words_equal=bool(out[2]), ints_equal=bool(out[3]),
+                    reals_equal=bool(out[4]), samples_equal=bool(out[5]), real0=r0.value)
+
+
 def load(build=True):
     if build:
         subprocess.run(["make", "-s", "-C", HERE], check=True)
