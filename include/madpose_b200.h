@@ -94,6 +94,8 @@ typedef struct mp_stats {
     uint64_t hypotheses_scored; /* models passed through scoring (minimal + LO) */
     uint64_t residual_evals;    /* sum over scored models of n */
     uint32_t lm_solves, lm_iterations;
+    uint64_t evals_fp64;     /* exact fp64 (model x match) evaluations: re-scoring, GetInliers, LO scoring */
+    uint64_t lm_block_evals; /* residual blocks evaluated (with Jacobian) over all LM iterations */
 } mp_stats;
 
 typedef struct mp_ctx mp_ctx;
@@ -111,6 +113,15 @@ int mp_measure_alu_peaks(mp_ctx *ctx, double *fp32_tflops, double *fp64_tflops);
  * list for data type t starts at 3*(n_0+...+n_{p-1}) + t*n_p. */
 int mp_estimate_batch(mp_ctx *ctx, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
                       const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers);
+/* The same in two steps, for callers that keep a batch resident in HBM: mp_upload_batch packs
+ * + copies the pairs and runs the front-end; mp_estimate_resident runs the loop on the resident
+ * batch (any number of times, e.g. with different options) and copies the results back. */
+int mp_upload_batch(mp_ctx *ctx, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt);
+int mp_estimate_resident(mp_ctx *ctx, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
+                         mp_stats *out_stats, int32_t *out_inliers);
+/* per kernel class of the last estimate call: device ms (CUDA events) and launch counts for
+ * {sampling, minimal solvers, fp32 scoring, decide (fp64 re-score + inliers + LO/LM)}; rounds */
+int mp_last_breakdown(mp_ctx *ctx, double *class_ms4, int *class_launches4, int *rounds);
 /* device time (ms, CUDA events on the launching stream) of the kernels of the last
  * mp_estimate_batch call, and the number of kernel launches it made */
 int mp_last_timing(mp_ctx *ctx, double *kernel_ms, double *total_ms, int *launches);

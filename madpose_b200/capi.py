@@ -87,6 +87,7 @@ class Stats(C.Structure):
         ("best_model_score", C.c_double), ("inlier_ratios", C.c_double * 3),
         ("hypotheses_scored", C.c_uint64), ("residual_evals", C.c_uint64),
         ("lm_solves", C.c_uint32), ("lm_iterations", C.c_uint32),
+        ("evals_fp64", C.c_uint64), ("lm_block_evals", C.c_uint64),
     ]
 
 
@@ -122,7 +123,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
-    "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
+    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
 ]
 
 
@@ -238,3 +239,23 @@ class Context:
             out.append([inl[o + t * p.n: o + t * p.n + s.num_inliers[t]].copy() for t in range(3)])
             o += 3 * p.n
         return models, list(stats), out
+
+    def upload_batch(self, kind, pairs, opt):
+        n = len(pairs)
+        self._resident = ((Pair * n)(*pairs), [p.n for p in pairs])
+        self._check(self.lib.mp_upload_batch(self.ctx, kind, n, self._resident[0], C.byref(opt)))
+
+    def estimate_resident(self, opt, cfg, want_inliers=True):
+        ns = self._resident[1]
+        n = len(ns)
+        models = np.zeros((n, MODEL_DOUBLES)); stats = (Stats * n)()
+        inl = np.zeros(3 * sum(ns) + 1, np.int32) if want_inliers else None
+        self._check(self.lib.mp_estimate_resident(self.ctx, C.byref(opt), C.byref(cfg), models.ctypes.data_as(C.c_void_p),
+                                                  stats, inl.ctypes.data_as(C.c_void_p) if want_inliers else None))
+        return models, stats, inl
+
+    def last_breakdown(self):
+        ms = (C.c_double * 4)(); ln = (C.c_int * 4)(); r = C.c_int()
+        self._check(self.lib.mp_last_breakdown(self.ctx, ms, ln, C.byref(r)))
+        names = ["sample", "minimal", "score", "decide"]
+        return {k: {"ms": ms[i], "launches": ln[i]} for i, k in enumerate(names)}, r.value

@@ -98,6 +98,7 @@ void mp_destroy(mp_ctx *c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+    for (auto &e : c->tick_ev) cudaEventDestroy(e);
     if (c->loop_alloc) delete static_cast<mp::LoopAlloc *>(c->loop_alloc);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;

@@ -24,18 +24,19 @@ __global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp
     o.reserved_ = 0;
     o.best_model_score = S.best_score;
     o.hypotheses_scored = S.hyps_scored; o.residual_evals = S.evals; o.lm_solves = S.lm_solves; o.lm_iterations = S.lm_iters;
+    o.evals_fp64 = S.evals64; o.lm_block_evals = S.lm_blocks;
     stats[p] = o;
 }
 
-static int run_estimate(mp_ctx *c, LoopAlloc &A, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
-                        const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers) {
+static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
+                        mp_stats *out_stats, int32_t *out_inliers, bool record_start) {
     if (opt->use_ours || opt->use_4p4d) return fail(MP_ERR_ARG, "use_ours / use_4p4d solvers are not implemented");
     if (opt->num_lsq_iterations < 0 || opt->num_lo_steps < 0 || opt->min_sample_multiplicator < 0)
         return fail(MP_ERR_ARG, "negative LO option");
+    if (c->resident_pairs <= 0) return fail(MP_ERR_ARG, "no resident batch: call mp_upload_batch first");
+    const int kind = c->resident_kind, n_pairs = c->resident_pairs;
     cudaStream_t s = c->stream;
-    MP_CUDA(cudaEventRecord(c->ev[0], s));
-    int rc = upload_pairs(c, kind, n_pairs, pairs, opt);
-    if (rc) return rc;
+    if (record_start) MP_CUDA(cudaEventRecord(c->ev[0], s));
     const long long N = c->total_n;
     // per-pair scratch capacities
     MP_CUDA(A.h_off3.reserve((n_pairs + 1) * sizeof(long long)));
@@ -48,11 +49,12 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, int kind, int n_pairs, const mp
     off3[0] = 0;
     int max_n = 32;
     for (int p = 0; p < n_pairs; p++) {
-        long long cap = 3ll * pairs[p].n + std::max<long long>(total_upper, 64) + 64;
+        const int np_ = (int)(c->off[p + 1] - c->off[p]);
+        long long cap = 3ll * np_ + std::max<long long>(total_upper, 64) + 64;
         if (cap > 2000000000ll) return fail(MP_ERR_ARG, "pair too large");
         caps[p] = (int)cap;
         off3[p + 1] = off3[p] + cap;
-        max_n = std::max(max_n, pairs[p].n);
+        max_n = std::max(max_n, np_);
     }
     const long long CAP = off3[n_pairs];
     const size_t slots = (size_t)n_pairs * LP_BMAX * LP_MM;
@@ -100,16 +102,35 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, int kind, int n_pairs, const mp
     const unsigned max_it = std::max(opt->max_num_iterations, opt->min_num_iterations);
     const long long max_rounds = 2ll * max_it + 64;
     long long rounds = 0;
+    c->n_tick = 0;
+    auto tick = [&](int cls) -> cudaError_t { // event before each kernel class; cls = -1 closes the last interval
+        if (c->n_tick >= (int)c->tick_ev.size()) {
+            cudaEvent_t ev;
+            cudaError_t e_ = cudaEventCreate(&ev);
+            if (e_ != cudaSuccess) return e_;
+            c->tick_ev.push_back(ev); c->tick_cls.push_back(0);
+        }
+        c->tick_cls[c->n_tick] = cls;
+        return cudaEventRecord(c->tick_ev[c->n_tick++], s);
+    };
     while (true) {
         MP_CUDA(cudaMemcpyAsync(h_active, A.misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
         MP_CUDA(cudaStreamSynchronize(s));
         if (*h_active <= 0) break;
         if (++rounds > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
+        MP_CUDA(tick(0));
         sample_kernel<<<(n_pairs + 31) / 32, 32, 0, s>>>(L, dprm);
+        MP_CUDA(tick(1));
         MP_CUDA(launch_minimal_batch(L, dprm, n_pairs, s));
-        if (kind == CALIB) MP_CUDA(launch_round_kind<CALIB>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
-        else if (kind == SHARED) MP_CUDA(launch_round_kind<SHARED>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
-        else MP_CUDA(launch_round_kind<TWO>(L, dprm, n_pairs, tile_cap, smem, A.off3.as<long long>(), A.caps.as<int>(), s));
+        MP_CUDA(tick(2));
+        if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, n_pairs, tile_cap, smem, s));
+        else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, n_pairs, tile_cap, smem, s));
+        else MP_CUDA(launch_score_kind<TWO>(L, dprm, n_pairs, tile_cap, smem, s));
+        MP_CUDA(tick(3));
+        if (kind == CALIB) MP_CUDA(launch_decide_kind<CALIB>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
+        else if (kind == SHARED) MP_CUDA(launch_decide_kind<SHARED>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
+        else MP_CUDA(launch_decide_kind<TWO>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
+        MP_CUDA(tick(-1));
         launches += 4;
     }
     finalize_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, n_pairs, A.out_models.as<mp_model>(), A.out_stats.as<mp_stats>());
@@ -127,6 +148,14 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, int kind, int n_pairs, const mp
     MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));
     c->last_kernel_ms = k; c->last_total_ms = t; c->last_launches = launches;
     c->last_rounds = (int)rounds;
+    for (int i = 0; i < 4; i++) { c->class_ms[i] = 0; c->class_launches[i] = 0; }
+    for (int i = 0; i + 1 < c->n_tick; i++) {
+        const int cls = c->tick_cls[i];
+        if (cls < 0) continue;
+        float ms = 0;
+        MP_CUDA(cudaEventElapsedTime(&ms, c->tick_ev[i], c->tick_ev[i + 1]));
+        c->class_ms[cls] += ms; c->class_launches[cls] += 1;
+    }
     return MP_OK;
 }
 
@@ -177,6 +206,25 @@ int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt,
     c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 2;
     return MP_OK;
 }
+int mp_upload_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt) {
+    using namespace mp;
+    if (!c || !pairs || !opt || n_pairs <= 0) return fail(MP_ERR_ARG, "mp_upload_batch: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    c->resident_pairs = 0;
+    int rc = upload_pairs(c, kind, n_pairs, pairs, opt);
+    if (rc) return rc;
+    MP_CUDA(cudaStreamSynchronize(c->stream));
+    c->resident_kind = kind; c->resident_pairs = n_pairs;
+    return MP_OK;
+}
+int mp_estimate_resident(mp_ctx *c, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
+                         mp_stats *out_stats, int32_t *out_inliers) {
+    using namespace mp;
+    if (!c || !opt || !cfg || !out_models || !out_stats) return fail(MP_ERR_ARG, "mp_estimate_resident: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    if (!c->loop_alloc) c->loop_alloc = new LoopAlloc();
+    return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, true);
+}
 int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt,
                       const mp_config *cfg, mp_model *out_models, mp_stats *out_stats, int32_t *out_inliers) {
     using namespace mp;
@@ -184,7 +232,21 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
         return fail(MP_ERR_ARG, "mp_estimate_batch: bad arguments");
     MP_CUDA(cudaSetDevice(c->device));
     if (!c->loop_alloc) c->loop_alloc = new LoopAlloc();
-    return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), kind, n_pairs, pairs, opt, cfg, out_models,
-                        out_stats, out_inliers);
+    c->resident_pairs = 0;
+    MP_CUDA(cudaEventRecord(c->ev[0], c->stream));
+    int rc = upload_pairs(c, kind, n_pairs, pairs, opt);
+    if (rc) return rc;
+    c->resident_kind = kind; c->resident_pairs = n_pairs;
+    return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, false);
+}
+int mp_last_breakdown(mp_ctx *c, double *class_ms4, int *class_launches4, int *rounds) {
+    using namespace mp;
+    if (!c) return fail(MP_ERR_ARG, "null context");
+    for (int i = 0; i < 4; i++) {
+        if (class_ms4) class_ms4[i] = c->class_ms[i];
+        if (class_launches4) class_launches4[i] = c->class_launches[i];
+    }
+    if (rounds) *rounds = c->last_rounds;
+    return MP_OK;
 }
 }

@@ -68,6 +68,12 @@ struct mp_ctx {
     long long total_n = 0, total32 = 0;
     double last_kernel_ms = 0, last_total_ms = 0;
     int last_launches = 0, last_rounds = 0;
+    int resident_kind = -1, resident_pairs = 0;
+    std::vector<cudaEvent_t> tick_ev;
+    std::vector<int> tick_cls;
+    int n_tick = 0;
+    double class_ms[4] = {0, 0, 0, 0};
+    int class_launches[4] = {0, 0, 0, 0};
     void *loop_alloc = nullptr; // mp::LoopAlloc, created on first mp_estimate_batch
     uint32_t tape_seed = 0;
     size_t tape_len = 0;

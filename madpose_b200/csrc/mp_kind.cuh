@@ -59,6 +59,7 @@ template <int KIND> __device__ void block_update_termination(const BlockCtx &C, 
     block_inliers(*C.pc, C.M, m, C.pc->thr, inl_best, sh->cnt, sh->wcnt);
     if (threadIdx.x == 0) {
         const int n = C.pc->n;
+        S->evals64 += n;
         S->best_num_inliers = sh->cnt[0] + sh->cnt[1] + sh->cnt[2];
         for (int t = 0; t < 3; t++) { S->num_inl[t] = sh->cnt[t]; S->ratios[t] = n > 0 ? (double)sh->cnt[t] / n : 0.0; }
         for (int s = 0; s < 2; s++)
@@ -117,6 +118,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kern
                     for (int j = 0; j < cnt; j++) {
                         if (!((cand >> j) & 1u)) continue;
                         const double sc = block_score64(pc, C.M, models[b * LP_MM + j], prm.cfg.score_type, sh.red);
+                        if (threadIdx.x == 0) S.evals64 += n;
                         if (sc < loc) { loc = sc; loc_id = j; }
                     }
                     const bool newbest = loc_id >= 0 && loc < S.best_min_score;
@@ -225,13 +227,15 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kern
 
 
 template <int KIND>
-cudaError_t launch_round_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, int tile_cap, size_t smem,
-                              const long long *off3, const int *caps, cudaStream_t s) {
+cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, int tile_cap, size_t smem, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(score_batch_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     score_batch_kernel<KIND><<<n_pairs, MP_CTA, smem, s>>>(L, dprm, tile_cap);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    return cudaGetLastError();
+}
+template <int KIND>
+cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, const long long *off3, const int *caps,
+                               cudaStream_t s) {
     decide_kernel<KIND><<<n_pairs, LP_THREADS, 0, s>>>(L, dprm, off3, caps);
     return cudaGetLastError();
 }
@@ -244,7 +248,7 @@ __global__ void __launch_bounds__(LP_THREADS, 1) lm_batch_kernel(const PairConst
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     const int j = blockIdx.x;
-    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; sh.m_tmp = start[j]; }
+    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; S.lm_blocks = 0; sh.m_tmp = start[j]; }
     __syncthreads();
     BlockCtx C;
     C.pc = pcp; C.M = M + pcp->off; C.prm = prmp; C.S = &S; C.rngB = nullptr; C.sh = &sh; C.cap = 0;

@@ -46,6 +46,7 @@ struct PairState {
     int number_lo, best_num_inliers, num_inl[3];
     double ratios[3];
     unsigned long long hyps_scored, evals;
+    unsigned long long evals64, lm_blocks; // fp64 (model x match) evaluations; LM residual-block evaluations
     unsigned lm_solves, lm_iters;
     int sizes[2][3], non_min_sample_size, min_sample_size;
 };

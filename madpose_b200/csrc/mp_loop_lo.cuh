@@ -46,6 +46,7 @@ template <int KIND> struct BlockEval {
             lm_block<KIND>(*C->pc, m, t, p, L->W, &a);
         }
         BlockScratch *sh = C->sh;
+        if (threadIdx.x == 0) C->S->lm_blocks += ntot;
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
         double *av = reinterpret_cast<double *>(&a);
         __syncthreads();
@@ -158,6 +159,7 @@ template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const doubl
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;
     block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt);
+    if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     const int *sz = C.S->sizes[solver];
     if (c0 < sz[0] || c1 < sz[1] || c2 < sz[2]) return;
@@ -182,7 +184,7 @@ template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const doubl
 // ScoreModel in fp64 + the work counters of the loop
 __device__ inline double block_score_counted(const BlockCtx &C, const Model &m) {
     const double s = block_score64(*C.pc, C.M, m, C.prm->cfg.score_type, C.sh->red);
-    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; }
+    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; }
     return s;
 }
 
@@ -211,6 +213,7 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
     update_best(sc, &sh->m_init);
     // base inliers of m_init at the nominal thresholds, flattened with type offsets
     block_inliers(pc, C.M, sh->m_init, pc.thr, C.inl_cur, sh->cnt, sh->wcnt);
+    if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
     for (int k = threadIdx.x; k < c1; k += blockDim.x) C.base[c0 + k] = C.inl_cur[n + k] + n;
