@@ -122,6 +122,9 @@ int mp_estimate_resident(mp_ctx *ctx, const mp_options *opt, const mp_config *cf
 /* per kernel class of the last estimate call: device ms (CUDA events) and launch counts for
  * {sampling, minimal solvers, fp32 scoring, decide (fp64 re-score + inliers + LO/LM)}; rounds */
 int mp_last_breakdown(mp_ctx *ctx, double *class_ms4, int *class_launches4, int *rounds);
+/* profiling aid: SM-clock cycles (one thread per pair's CTA, summed over pairs) the decide kernel spent in
+ * {sequential scan, GetInliers, fp64 ScoreModel, LM evaluation, LM solves total, shuffles, un-flatten, LO total} */
+int mp_last_phase_cycles(mp_ctx *ctx, unsigned long long *cycles8);
 /* device time (ms, CUDA events on the launching stream) of the kernels of the last
  * mp_estimate_batch call, and the number of kernel launches it made */
 int mp_last_timing(mp_ctx *ctx, double *kernel_ms, double *total_ms, int *launches);

@@ -68,7 +68,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.inl_cur.reserve((3 * (size_t)N + 4) * sizeof(int)));
     MP_CUDA(A.flat.reserve(2 * (size_t)CAP * sizeof(int)));
     MP_CUDA(A.sample.reserve(3 * (size_t)CAP * sizeof(int)));
-    MP_CUDA(A.misc.reserve(64));
+    MP_CUDA(A.misc.reserve(256));
     MP_CUDA(A.off3.reserve((n_pairs + 1) * sizeof(long long)));
     MP_CUDA(A.caps.reserve(n_pairs * sizeof(int)));
     MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
@@ -90,6 +90,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.models = A.models.as<Model>(); L.hyps = A.hyps.as<HypF>();
     L.inl_best = A.inl_best.as<int>(); L.inl_cur = A.inl_cur.as<int>(); L.flat = A.flat.as<int>(); L.sample = A.sample.as<int>();
     L.n_active = A.misc.as<int>();
+    L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>() + 64);
+    MP_CUDA(cudaMemsetAsync(L.clk, 0, 64, s));
     const LoopParams *dprm = A.prm.as<LoopParams>();
     MP_CUDA(cudaEventRecord(c->ev[1], s));
     init_state_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, dprm);
@@ -139,6 +141,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaEventRecord(c->ev[2], s));
     MP_CUDA(cudaMemcpyAsync(out_models, A.out_models.p, n_pairs * sizeof(mp_model), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(out_stats, A.out_stats.p, n_pairs * sizeof(mp_stats), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(c->phase_clk, L.clk, 64, cudaMemcpyDeviceToHost, s));
     if (out_inliers && N > 0)
         MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, 3 * (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaEventRecord(c->ev[3], s));
@@ -238,6 +241,12 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
     if (rc) return rc;
     c->resident_kind = kind; c->resident_pairs = n_pairs;
     return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, false);
+}
+int mp_last_phase_cycles(mp_ctx *c, unsigned long long *cycles8) {
+    using namespace mp;
+    if (!c || !cycles8) return fail(MP_ERR_ARG, "null argument");
+    for (int i = 0; i < 8; i++) cycles8[i] = c->phase_clk[i];
+    return MP_OK;
 }
 int mp_last_breakdown(mp_ctx *c, double *class_ms4, int *class_launches4, int *rounds) {
     using namespace mp;

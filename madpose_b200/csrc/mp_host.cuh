@@ -72,6 +72,7 @@ struct mp_ctx {
     std::vector<cudaEvent_t> tick_ev;
     std::vector<int> tick_cls;
     int n_tick = 0;
+    unsigned long long phase_clk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     void *loop_alloc = nullptr; // mp::LoopAlloc, created on first mp_estimate_batch

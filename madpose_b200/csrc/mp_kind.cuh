@@ -69,7 +69,7 @@ template <int KIND> __device__ void block_update_termination(const BlockCtx &C, 
     __syncthreads();
 }
 
-template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kernel(LoopBuffers L, const LoopParams *prmp,
+template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) decide_kernel(LoopBuffers L, const LoopParams *prmp,
                                                                                   const long long *off3, const int *caps) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
@@ -100,6 +100,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kern
     const int n = pc.n;
 
     if (S.phase == PH_ITER) {
+        const long long scan_t0 = clock64();
         bool lo_event = false;
         for (int b = 0; b < S.batch_len; b++) {
             const unsigned it = S.it;
@@ -166,6 +167,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kern
                 S.B = min(prm.bmax, S.B * 2);
             }
         } else if (lo_event && threadIdx.x == 0) S.B = max(4, prm.bmax / 4);
+        if (threadIdx.x == 0) S.clk[0] += (unsigned long long)(clock64() - scan_t0);
         __syncthreads();
     }
 
@@ -222,7 +224,10 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, 1) decide_kern
         const int *src = reinterpret_cast<const int *>(&S);
         for (int i = threadIdx.x; i < (int)(sizeof(PairState) / 4); i += blockDim.x) dst[i] = src[i];
     }
-    if (threadIdx.x == 0 && S.phase == PH_DONE) atomicSub(L.n_active, 1);
+    if (threadIdx.x == 0 && S.phase == PH_DONE) {
+        atomicSub(L.n_active, 1);
+        for (int q = 0; q < 8; q++) atomicAdd(L.clk + q, S.clk[q]);
+    }
 }
 
 
@@ -242,29 +247,26 @@ cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int n_pair
 
 // mp_lm_batch: one CTA per LM problem of one pair
 template <int KIND>
-__global__ void __launch_bounds__(LP_THREADS, 1) lm_batch_kernel(const PairConst *pcp, const Match64 *M, const LoopParams *prmp,
+__global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lm_batch_kernel(const PairConst *pcp, const Match64 *M, const LoopParams *prmp,
                                                                   int n_problems, const Model *start, const int *idx,
                                                                   const int *off, Model *out, double *info) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     const int j = blockIdx.x;
-    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; S.lm_blocks = 0; sh.m_tmp = start[j]; }
+    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; S.lm_blocks = 0; for (int q = 0; q < 8; q++) S.clk[q] = 0; sh.m_tmp = start[j]; }
     __syncthreads();
     BlockCtx C;
     C.pc = pcp; C.M = M + pcp->off; C.prm = prmp; C.S = &S; C.rngB = nullptr; C.sh = &sh; C.cap = 0;
     C.inl_cur = nullptr; C.flat = nullptr; C.base = nullptr; C.sample = nullptr;
     const int *l0 = idx + off[3 * j], *l1 = idx + off[3 * j + 1], *l2 = idx + off[3 * j + 2];
     const int n0 = off[3 * j + 1] - off[3 * j], n1 = off[3 * j + 2] - off[3 * j + 1], n2 = off[3 * j + 3] - off[3 * j + 2];
-    LmSetup L;
-    LmInfo inf = {0, 0, 0, 0};
-    if (lm_setup(*pcp, prmp->cfg, n0, n1, n2, &L)) {
+    __shared__ LmInfo inf;
+    if (threadIdx.x == 0) { inf = LmInfo{0, 0, 0, 0}; sh.lm_go = lm_setup(*pcp, prmp->cfg, n0, n1, n2, &sh.lm_setup) ? 1 : 0; }
+    __syncthreads();
+    if (sh.lm_go) {
         BlockEval<KIND> ev;
-        ev.C = &C; ev.L = &L; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
-        double x[LM_NA];
-        lm_model_to_x(sh.m_tmp, x);
-        lm_minimize(L, ev, x, &inf);
-        __syncthreads();
-        if (threadIdx.x == 0) lm_x_to_model(KIND, x, &sh.m_tmp);
+        ev.C = &C; ev.L = &sh.lm_setup; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
+        block_lm<KIND>(C, sh.lm_setup, ev, sh.m_tmp, &sh.m_tmp, &inf);
     }
     __syncthreads();
     if (threadIdx.x == 0) {

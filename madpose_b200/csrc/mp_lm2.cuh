@@ -98,67 +98,94 @@ MP_HD double lm_compress(const LmSetup &L, const LmAcc &acc, double *A, double *
     return acc.cost;
 }
 
-// Ev: void operator()(const double *x, LmAcc *reduced)   (collective on the device)
-template <class Ev> MP_HD void lm_minimize(const LmSetup &L, Ev &ev, double *x, LmInfo *info) {
-    info->iterations = 0; info->termination = 0; info->cost0 = 0; info->cost = 0;
-    for (int k = 0; k < LM_NA; k++)
-        if (L.has_lower[k] && x[k] < L.lower[k]) { info->termination = 4; return; }
-    const int nt = L.nt;
-    double A[LM_NT * LM_NT], g[LM_NT], An[LM_NT * LM_NT], gn[LM_NT], scale[LM_NT];
-    LmAcc acc;
-    ev(x, &acc);
-    double cost = lm_compress(L, acc, A, g);
-    info->cost0 = cost; info->cost = cost;
-    for (int a = 0; a < nt; a++) scale[a] = 1.0 / (1.0 + sqrt(A[a * nt + a]));
-    auto grad_max = [&](const double *xx, const double *gg) {
+// The LM iteration as a state machine, so that ONE thread of a CTA can drive it while the whole
+// CTA evaluates (cost, J^T J, J^T r) at the points it asks for:
+//   begin(x0) -> evaluate at x -> first(acc) -> { propose() -> evaluate at xc -> feed(acc) }*
+struct LmDriver {
+    const LmSetup *L;
+    LmInfo info;
+    double x[LM_NA], xc[LM_NA];
+    double A[LM_NT * LM_NT], g[LM_NT], As[LM_NT * LM_NT], gs[LM_NT], scale[LM_NT];
+    double Ad[LM_NT * LM_NT], Lc[LM_NT * LM_NT], An[LM_NT * LM_NT], gn[LM_NT], y[LM_NT], yw[LM_NT]; // workspace (kept
+    // in the object so that a driver placed in shared memory does all its array work there)
+    double cost, radius, decrease, mcc;
+    double min_cost, cur_cost, ref_cost, cand_cost, acc_ref, acc_cand;
+    int n_nonmono, n_invalid, it;
+
+    MP_HD double grad_max(const double *xx, const double *gg) const {
         double d[LM_NT], xp[LM_NA], mx = 0;
-        for (int a = 0; a < nt; a++) d[a] = -gg[a];
-        lm_plus(L, xx, d, xp);
+        for (int a = 0; a < L->nt; a++) d[a] = -gg[a];
+        lm_plus(*L, xx, d, xp);
         for (int k = 0; k < LM_NA; k++) mx = fmax(mx, fabs(xp[k] - xx[k]));
         return mx;
-    };
-    if (!finite_d(cost)) { info->termination = 3; return; }
-    if (grad_max(x, g) <= L.gtol) { info->termination = 1; return; }
-    double radius = 1e4, decrease = 2.0;
-    double min_cost = cost, cur_cost = cost, ref_cost = cost, cand_cost = cost, acc_ref = 0, acc_cand = 0;
-    int n_nonmono = 0, n_invalid = 0;
-    info->termination = 2;
-    for (int it = 1; it <= L.max_it; it++) {
-        info->iterations = it;
-        if (radius < 1e-32) { info->termination = 1; break; }
-        double As[LM_NT * LM_NT], Ad[LM_NT * LM_NT], gs[LM_NT], y[LM_NT];
-        for (int a = 0; a < nt; a++) {
-            gs[a] = g[a] * scale[a];
-            for (int b = 0; b < nt; b++) { As[a * nt + b] = A[a * nt + b] * scale[a] * scale[b]; Ad[a * nt + b] = As[a * nt + b]; }
-        }
-        for (int a = 0; a < nt; a++) Ad[a * nt + a] += fmin(fmax(As[a * nt + a], 1e-6), 1e32) / radius;
-        const bool ok = cholesky_solve<LM_NT>(nt, Ad, gs, y);
-        double mcc = 0;
-        if (ok) {
-            for (int a = 0; a < nt; a++) y[a] = -y[a];
-            double dg = 0, dAd = 0;
+    }
+    // false: infeasible start, nothing to do (termination 4)
+    MP_HD bool begin(const LmSetup *Lp, const double *x0) {
+        L = Lp;
+        info.iterations = 0; info.termination = 0; info.cost0 = 0; info.cost = 0;
+        for (int k = 0; k < LM_NA; k++) x[k] = x0[k];
+        for (int k = 0; k < LM_NA; k++)
+            if (L->has_lower[k] && x[k] < L->lower[k]) { info.termination = 4; return false; }
+        return true;
+    }
+    // evaluation at the start point; false: finished
+    MP_HD bool first(const LmAcc &acc) {
+        const int nt = L->nt;
+        cost = lm_compress(*L, acc, A, g);
+        info.cost0 = cost; info.cost = cost;
+        for (int a = 0; a < nt; a++) scale[a] = 1.0 / (1.0 + sqrt(A[a * nt + a]));
+        if (!finite_d(cost)) { info.termination = 3; return false; }
+        if (grad_max(x, g) <= L->gtol) { info.termination = 1; return false; }
+        radius = 1e4; decrease = 2.0;
+        min_cost = cur_cost = ref_cost = cand_cost = cost; acc_ref = 0; acc_cand = 0;
+        n_nonmono = 0; n_invalid = 0; it = 0;
+        info.termination = 2;
+        return true;
+    }
+    // next candidate xc; false: finished (max iterations / radius / repeated invalid steps)
+    MP_HD bool propose() {
+        const int nt = L->nt;
+        while (true) {
+            if (++it > L->max_it) { info.cost = cost; return false; }
+            info.iterations = it;
+            if (radius < 1e-32) { info.termination = 1; info.cost = cost; return false; }
             for (int a = 0; a < nt; a++) {
-                dg += y[a] * gs[a];
-                for (int b = 0; b < nt; b++) dAd += y[a] * As[a * nt + b] * y[b];
+                gs[a] = g[a] * scale[a];
+                for (int b = 0; b < nt; b++) { As[a * nt + b] = A[a * nt + b] * scale[a] * scale[b]; Ad[a * nt + b] = As[a * nt + b]; }
             }
-            mcc = -(dg + 0.5 * dAd);
+            for (int a = 0; a < nt; a++) Ad[a * nt + a] += fmin(fmax(As[a * nt + a], 1e-6), 1e32) / radius;
+            const bool ok = cholesky_solve_ws(nt, Ad, gs, y, Lc, yw);
+            mcc = 0;
+            if (ok) {
+                for (int a = 0; a < nt; a++) y[a] = -y[a];
+                double dg = 0, dAd = 0;
+                for (int a = 0; a < nt; a++) {
+                    dg += y[a] * gs[a];
+                    for (int b = 0; b < nt; b++) dAd += y[a] * As[a * nt + b] * y[b];
+                }
+                mcc = -(dg + 0.5 * dAd);
+            }
+            if (!ok || !(mcc > 0)) {
+                if (++n_invalid >= 5) { info.termination = 3; info.cost = cost; return false; }
+                radius /= decrease; decrease *= 2;
+                continue;
+            }
+            n_invalid = 0;
+            double d[LM_NT];
+            for (int a = 0; a < nt; a++) d[a] = y[a] * scale[a];
+            lm_plus(*L, x, d, xc);
+            return true;
         }
-        if (!ok || !(mcc > 0)) {
-            if (++n_invalid >= 5) { info->termination = 3; break; }
-            radius /= decrease; decrease *= 2;
-            continue;
-        }
-        n_invalid = 0;
-        double d[LM_NT], xc[LM_NA];
-        for (int a = 0; a < nt; a++) d[a] = y[a] * scale[a];
-        lm_plus(L, x, d, xc);
-        ev(xc, &acc);
-        double cc = lm_compress(L, acc, An, gn);
+    }
+    // evaluation at xc; false: converged
+    MP_HD bool feed(const LmAcc &acc) {
+        const int nt = L->nt;
+        double cc = lm_compress(*L, acc, An, gn);
         if (!finite_d(cc)) cc = DBL_MAX;
         double sn = 0, xn = 0;
         for (int k = 0; k < LM_NA; k++) { sn += (xc[k] - x[k]) * (xc[k] - x[k]); xn += x[k] * x[k]; }
-        if (sqrt(sn) <= L.ptol * (sqrt(xn) + L.ptol)) { info->termination = 1; break; }
-        if (fabs(cost - cc) <= L.ftol * cost) { info->termination = 1; break; }
+        if (sqrt(sn) <= L->ptol * (sqrt(xn) + L->ptol)) { info.termination = 1; info.cost = cost; return false; }
+        if (fabs(cost - cc) <= L->ftol * cost) { info.termination = 1; info.cost = cost; return false; }
         const double rel = cc >= DBL_MAX ? -DBL_MAX : fmax((cur_cost - cc) / mcc, (ref_cost - cc) / (acc_ref + mcc));
         if (rel > 1e-3) {
             for (int k = 0; k < LM_NA; k++) x[k] = xc[k];
@@ -171,13 +198,29 @@ template <class Ev> MP_HD void lm_minimize(const LmSetup &L, Ev &ev, double *x, 
             cur_cost = cc; acc_cand += mcc; acc_ref += mcc;
             if (cur_cost < min_cost) { min_cost = cur_cost; n_nonmono = 0; cand_cost = cur_cost; acc_cand = 0; }
             else { ++n_nonmono; if (cur_cost > cand_cost) { cand_cost = cur_cost; acc_cand = 0; } }
-            if (n_nonmono == L.max_nonmono) { ref_cost = cand_cost; acc_ref = acc_cand; }
-            if (grad_max(x, g) <= L.gtol) { info->termination = 1; break; }
+            if (n_nonmono == L->max_nonmono) { ref_cost = cand_cost; acc_ref = acc_cand; }
+            if (grad_max(x, g) <= L->gtol) { info.termination = 1; info.cost = cost; return false; }
         } else {
             radius /= decrease; decrease *= 2;
         }
+        return true;
     }
-    info->cost = cost;
+};
+
+// single-thread form (host check): Ev: void operator()(const double *x, LmAcc *sums)
+template <class Ev> MP_HD void lm_minimize(const LmSetup &L, Ev &ev, double *x, LmInfo *info) {
+    LmDriver drv;
+    LmAcc acc;
+    if (drv.begin(&L, x)) {
+        ev(drv.x, &acc);
+        if (drv.first(acc))
+            while (drv.propose()) {
+                ev(drv.xc, &acc);
+                if (!drv.feed(acc)) break;
+            }
+    }
+    for (int k = 0; k < LM_NA; k++) x[k] = drv.x[k];
+    *info = drv.info;
 }
 
 } // namespace mp

@@ -23,7 +23,8 @@ namespace mp {
 
 constexpr int LP_BMAX = 32;            // iterations per pair per round (upper bound)
 constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
-constexpr int LP_THREADS = 256;        // decide_kernel CTA
+constexpr int LP_THREADS = 128;        // decide_kernel CTA
+constexpr int LP_CTAS_PER_SM = 2;
 enum { PH_ITER = 0, PH_LO_PRE = 1, PH_LO_MAIN = 2, PH_FINISH = 3, PH_DONE = 4 };
 
 struct LoopParams {
@@ -49,6 +50,7 @@ struct PairState {
     unsigned long long evals64, lm_blocks; // fp64 (model x match) evaluations; LM residual-block evaluations
     unsigned lm_solves, lm_iters;
     int sizes[2][3], non_min_sample_size, min_sample_size;
+    unsigned long long clk[8]; // SM-clock cycles of thread 0 per phase: 0 scan 1 inliers 2 score64 3 lm eval 4 lm driver 5 shuffle 6 unflatten 7 LO total
 };
 
 // per-pair work buffers of one round
@@ -74,6 +76,7 @@ struct LoopBuffers {
     int *flat;      // [3 * off + pad] scratch: flattened inlier list / shuffled sample
     int *sample;    // [3 * off + pad] scratch: un-flattened sample lists
     int *n_active;  // device counter of pairs not yet PH_DONE
+    unsigned long long *clk; // [8] phase cycle totals over all pairs (profiling aid)
 };
 
 // ---------------------------------------------------------------- block-level helpers

@@ -6,6 +6,11 @@
 
 namespace mp {
 
+#define MP_CLK_BEGIN() const long long clk_t0_ = clock64()
+#define MP_CLK_END(C_, slot_) do { if (threadIdx.x == 0) (C_).S->clk[slot_] += (unsigned long long)(clock64() - clk_t0_); } while (0)
+
+constexpr int SH_MAXHEAD = 1024, SH_TAB = 2048;
+
 struct BlockScratch { // shared memory of the decide kernel
     double red[32];
     double part[LP_THREADS / 32][LM_ACC_DOUBLES];
@@ -13,6 +18,14 @@ struct BlockScratch { // shared memory of the decide kernel
     int cnt[3], wcnt[3][16];
     int flag[4], base_len, fit_len, fit_cnt[3];
     Model m_lo, m_init, m_tmp;
+    // LM: the point the CTA evaluates next and the driver's verdict (written by thread 0)
+    double lm_x[LM_NA];
+    int lm_go;
+    LmSetup lm_setup;
+    LmDriver drv;
+    // fast Fisher-Yates head: draws, prefetched values, displaced-position hash table
+    int sh_j[SH_MAXHEAD], sh_vi[SH_MAXHEAD], sh_vj[SH_MAXHEAD];
+    int sh_key[SH_TAB], sh_val[SH_TAB];
 };
 
 struct BlockCtx {
@@ -26,15 +39,17 @@ struct BlockCtx {
     BlockScratch *sh;
 };
 
-// ---- collective evaluation of cost, J^T J, J^T r
+// ---- collective evaluation of cost, J^T J, J^T r at sh->lm_x; the sums are left in sh->total
 template <int KIND> struct BlockEval {
     const BlockCtx *C;
     const LmSetup *L;
     const int *lst[3];
     int n[3];
-    __device__ void operator()(const double *x, LmAcc *out) const {
+    __device__ void operator()() const {
+        MP_CLK_BEGIN();
+        BlockScratch *sh = C->sh;
         LmPoint p;
-        lm_point(KIND, x, &p);
+        lm_point(KIND, sh->lm_x, &p);
         LmAcc a;
         a.clear();
         const int n0 = L->use_reproj ? n[0] : 0, n1 = L->use_reproj ? n[1] : 0, n2 = L->use_samp ? n[2] : 0;
@@ -45,11 +60,9 @@ template <int KIND> struct BlockEval {
             const Match64 m = C->M[lst[t][k]];
             lm_block<KIND>(*C->pc, m, t, p, L->W, &a);
         }
-        BlockScratch *sh = C->sh;
         if (threadIdx.x == 0) C->S->lm_blocks += ntot;
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
         double *av = reinterpret_cast<double *>(&a);
-        __syncthreads();
 #pragma unroll
         for (int v = 0; v < LM_ACC_DOUBLES; v++) {
             double s = av[v];
@@ -64,49 +77,98 @@ template <int KIND> struct BlockEval {
             sh->total[threadIdx.x] = s;
         }
         __syncthreads();
-        double *ov = reinterpret_cast<double *>(out);
-        for (int v = 0; v < LM_ACC_DOUBLES; v++) ov[v] = sh->total[v];
+        MP_CLK_END(*C, 3);
     }
 };
 static_assert(sizeof(LmAcc) == LM_ACC_DOUBLES * sizeof(double), "LmAcc is a flat array of doubles");
 
+// One LM solve by the CTA: thread 0 runs the driver (LmDriver), everybody evaluates.
+// x0 -> x (final parameters, valid on thread 0 only); returns info on thread 0.
+template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L, const BlockEval<KIND> &ev,
+                                             const Model &start, Model *out, LmInfo *info_out) {
+    MP_CLK_BEGIN();
+    BlockScratch *sh = C.sh;
+    LmDriver &drv = sh->drv; // driven by thread 0 only; shared memory keeps its arrays off the local-memory path
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double x0[LM_NA];
+        lm_model_to_x(start, x0);
+        sh->lm_go = drv.begin(&L, x0) ? 1 : 0;
+        for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.x[k];
+    }
+    __syncthreads();
+    if (sh->lm_go) {
+        ev();
+        if (threadIdx.x == 0) {
+            const bool go = drv.first(*reinterpret_cast<const LmAcc *>(sh->total)) && drv.propose();
+            sh->lm_go = go ? 1 : 0;
+            for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.xc[k];
+        }
+        __syncthreads();
+        while (sh->lm_go) {
+            ev();
+            if (threadIdx.x == 0) {
+                const bool go = drv.feed(*reinterpret_cast<const LmAcc *>(sh->total)) && drv.propose();
+                sh->lm_go = go ? 1 : 0;
+                for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.xc[k];
+            }
+            __syncthreads();
+        }
+    }
+    if (threadIdx.x == 0) {
+        Model m = start;
+        lm_x_to_model(KIND, drv.x, &m);
+        *out = m;
+        *info_out = drv.info;
+    }
+    __syncthreads();
+    MP_CLK_END(C, 4);
+}
+
 // NonMinimalSolver / LeastSquares on explicit lists; *m is a shared-memory model.
 template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, int n0, const int *l1, int n1,
                                               const int *l2, int n2, Model *m) {
-    LmSetup L;
-    if (!lm_setup(*C.pc, C.prm->cfg, n0, n1, n2, &L)) return;
+    BlockScratch *sh = C.sh;
+    __syncthreads();
+    if (threadIdx.x == 0) sh->lm_go = lm_setup(*C.pc, C.prm->cfg, n0, n1, n2, &sh->lm_setup) ? 1 : 0;
+    __syncthreads();
+    if (!sh->lm_go) return;
     BlockEval<KIND> ev;
-    ev.C = &C; ev.L = &L; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
-    double x[LM_NA];
-    LmInfo info;
-    __syncthreads();
-    lm_model_to_x(*m, x);
-    lm_minimize(L, ev, x, &info);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        lm_x_to_model(KIND, x, m);
-        C.S->lm_solves += 1; C.S->lm_iters += info.iterations;
-    }
+    ev.C = &C; ev.L = &sh->lm_setup; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
+    __shared__ LmInfo info;
+    block_lm<KIND>(C, sh->lm_setup, ev, *m, m, &info);
+    if (threadIdx.x == 0) { C.S->lm_solves += 1; C.S->lm_iters += info.iterations; }
     __syncthreads();
 }
 
 // utils::RandomShuffleAndResize (ext/RansacLib/RansacLib/utils.h:48-73) on v[0..*len) with
-// stream B.  Positions < target are final after `target` swap steps; the remaining steps
-// only consume random words, which the CTA checks in parallel for Lemire rejections.
+// stream B: for i in 0..n-2: swap(v[i], v[uniform_int(i, n-1)]), then resize(target).
+// Only the first `target` outputs survive the resize and position i is final after step i, so
+//  (1) ALL n-1 draws are evaluated in parallel straight from the generator ring (draw i uses
+//      word pos+i unless an earlier draw hit a Lemire rejection, which is detected in parallel
+//      and resolved sequentially for that one draw);
+//  (2) the first head = min(target, n-1) swaps are replayed by one thread on shared memory
+//      only: prefetched original values + a small hash table of displaced positions.
 __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *v, int *len_sh) {
+    MP_CLK_BEGIN();
     MtStream *g = C.rngB;
+    BlockScratch *sh = C.sh;
     __syncthreads();
     const int n = *len_sh;
     __syncthreads();
     const int head = n - 1 < target ? (n - 1 > 0 ? n - 1 : 0) : target;
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < head; i++) {
-            const int j = mt_uniform_int(g, i, n - 1);
-            const int t = v[i]; v[i] = v[j]; v[j] = t;
-        }
+    const bool fast = head <= SH_MAXHEAD;
+    if (!fast) {
+        if (threadIdx.x == 0)
+            for (int i = 0; i < head; i++) {
+                const int j = mt_uniform_int(g, i, n - 1);
+                const int t = v[i]; v[i] = v[j]; v[j] = t;
+            }
+        __syncthreads();
+    } else {
+        for (int k = threadIdx.x; k < SH_TAB; k += blockDim.x) sh->sh_key[k] = -1;
     }
-    __syncthreads();
-    int i = head; // remaining draws: uniform_int(i, n-1) for i in [head, n-1)
+    int i = fast ? 0 : head; // draws still to take: uniform_int(i, n-1) for i in [i, n-1)
     while (i < n - 1) {
         if (g->pos == g->gen) mt_refill(g, (int)threadIdx.x, (int)blockDim.x, [] { __syncthreads(); });
         const unsigned long long pos = g->pos;
@@ -117,40 +179,97 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
             if (mt_lemire_rejects(w, (uint32_t)(n - (i + j)))) { first = j; break; }
         }
         __syncthreads();
-        if (threadIdx.x == 0) C.sh->flag[0] = m;
+        if (threadIdx.x == 0) sh->flag[0] = m;
         __syncthreads();
-        if (first < m) atomicMin(&C.sh->flag[0], first);
+        if (first < m) atomicMin(&sh->flag[0], first);
         __syncthreads();
-        first = C.sh->flag[0];
+        first = sh->flag[0];
+        if (fast) // draws [i, i+first) are valid: record those of the head
+            for (int j = threadIdx.x; j < first && i + j < head; j += blockDim.x) {
+                const uint32_t w = mt_temper(g->x[(pos + j) % MT_RING]);
+                const int ii = i + j, jj = ii + (int)(((unsigned long long)w * (uint32_t)(n - ii)) >> 32);
+                sh->sh_j[ii] = jj; sh->sh_vi[ii] = v[ii]; sh->sh_vj[ii] = v[jj];
+            }
         __syncthreads();
         if (threadIdx.x == 0) {
             g->pos = pos + first;
-            if (first < m) (void)mt_uniform_int(g, i + first, n - 1); // the draw with a rejection, sequentially
+            if (first < m) { // the draw with a rejection, sequentially
+                const int ii = i + first, jj = mt_uniform_int(g, ii, n - 1);
+                if (fast && ii < head) { sh->sh_j[ii] = jj; sh->sh_vi[ii] = v[ii]; sh->sh_vj[ii] = v[jj]; }
+            }
         }
         i += first + (first < m ? 1 : 0);
         __syncthreads();
     }
+    if (fast && threadIdx.x == 0) {
+        auto slot = [&](int key) { // open addressing, linear probing; returns the slot holding key or the free one
+            unsigned h = ((unsigned)key * 2654435761u) >> 21;
+            while (sh->sh_key[h] != -1 && sh->sh_key[h] != key) h = (h + 1) & (SH_TAB - 1);
+            return (int)h;
+        };
+        for (int k = 0; k < head; k++) {
+            const int j = sh->sh_j[k];
+            int h = slot(k);
+            const int a = sh->sh_key[h] == k ? sh->sh_val[h] : sh->sh_vi[k];
+            int b = a;
+            if (j != k) {
+                h = slot(j);
+                b = sh->sh_key[h] == j ? sh->sh_val[h] : sh->sh_vj[k];
+                sh->sh_key[h] = j; sh->sh_val[h] = a;
+            }
+            v[k] = b;
+        }
+        if (head == n - 1 && n - 1 < target && n >= 1) { // the list grows: its last element is kept too
+            const int h = slot(n - 1);
+            if (sh->sh_key[h] == n - 1) v[n - 1] = sh->sh_val[h];
+        }
+    }
+    __syncthreads();
     // resize: shrink, or grow with zeros (quirk Q3)
     for (int k = n + threadIdx.x; k < target; k += blockDim.x) v[k] = 0;
     __syncthreads();
     if (threadIdx.x == 0) *len_sh = target;
     __syncthreads();
+    MP_CLK_END(C, 5);
 }
 
-// un-flatten (hybrid_ransac.h:443-449, 528-534): entry e -> (type e / n, index e % n), order kept
+// un-flatten (hybrid_ransac.h:443-449, 528-534): entry e -> (type e / n, index e % n), order kept.
+// Stable three-way partition by ballot + prefix counts, one chunk of blockDim entries at a time.
 __device__ inline void block_unflatten(const BlockCtx &C, const int *flat, int len, int *cnt3_sh) {
+    MP_CLK_BEGIN();
+    BlockScratch *sh = C.sh;
     const int n = C.pc->n;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        int c[3] = {0, 0, 0};
-        for (int k = 0; k < len; k++) {
-            int e = flat[k], t = 0;
+    if (threadIdx.x < 3) cnt3_sh[threadIdx.x] = 0;
+    __syncthreads();
+    for (int start = 0; start < len; start += blockDim.x) {
+        const int k = start + threadIdx.x;
+        int e = 0, t = -1;
+        if (k < len) {
+            e = flat[k]; t = 0;
             while (e >= n && t < 2) { e -= n; t++; }
-            C.sample[t * C.cap + c[t]++] = e;
         }
-        cnt3_sh[0] = c[0]; cnt3_sh[1] = c[1]; cnt3_sh[2] = c[2];
+        unsigned bal[3];
+        for (int q = 0; q < 3; q++) {
+            bal[q] = __ballot_sync(0xffffffffu, t == q);
+            if (lane == 0) sh->wcnt[q][warp] = __popc(bal[q]);
+        }
+        __syncthreads();
+        if (t >= 0) {
+            int off = cnt3_sh[t];
+            for (int w = 0; w < warp; w++) off += sh->wcnt[t][w];
+            C.sample[t * C.cap + off + __popc(bal[t] & ((1u << lane) - 1u))] = e;
+        }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            int c = 0;
+            for (int w = 0; w < nw; w++) c += sh->wcnt[threadIdx.x][w];
+            cnt3_sh[threadIdx.x] += c;
+        }
+        __syncthreads();
     }
-    __syncthreads();
+    MP_CLK_END(C, 6);
 }
 
 // LeastSquaresFit (hybrid_ransac.h:484-538)
@@ -158,7 +277,7 @@ template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const doubl
                                                   bool all_inliers) {
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;
-    block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt);
+    { MP_CLK_BEGIN(); block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
     if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     const int *sz = C.S->sizes[solver];
@@ -183,7 +302,9 @@ template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const doubl
 
 // ScoreModel in fp64 + the work counters of the loop
 __device__ inline double block_score_counted(const BlockCtx &C, const Model &m) {
+    MP_CLK_BEGIN();
     const double s = block_score64(*C.pc, C.M, m, C.prm->cfg.score_type, C.sh->red);
+    MP_CLK_END(C, 2);
     if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; }
     return s;
 }
@@ -191,6 +312,7 @@ __device__ inline double block_score_counted(const BlockCtx &C, const Model &m) 
 // LocalOptimization (hybrid_ransac.h:383-482).  best / best_score / best_solver live in shared memory.
 template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, int solver, Model *best,
                                                              double *best_score, int *best_solver) {
+    MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
     const PairConst &pc = *C.pc;
     const mp_options &o = C.prm->opt;
@@ -212,7 +334,7 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
     double sc = block_score_counted(C, sh->m_init);
     update_best(sc, &sh->m_init);
     // base inliers of m_init at the nominal thresholds, flattened with type offsets
-    block_inliers(pc, C.M, sh->m_init, pc.thr, C.inl_cur, sh->cnt, sh->wcnt);
+    { MP_CLK_BEGIN(); block_inliers(pc, C.M, sh->m_init, pc.thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
     if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
@@ -254,6 +376,7 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
         }
     }
     __syncthreads();
+    MP_CLK_END(C, 7);
 }
 
 } // namespace mp

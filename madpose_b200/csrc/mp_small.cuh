@@ -167,8 +167,8 @@ template <int M, int N> MP_HD void nullspace_qr(const double *A, double *basis) 
 }
 
 // Cholesky solve of the SPD system A x = b (n <= NMAX, A row-major with leading dim n).
-template <int NMAX> MP_HD bool cholesky_solve(int n, const double *A, const double *b, double *x) {
-    double L[NMAX * NMAX], y[NMAX];
+// (L: n*n doubles, y: n doubles of caller workspace)
+MP_HD bool cholesky_solve_ws(int n, const double *A, const double *b, double *x, double *L, double *y) {
     for (int i = 0; i < n; i++)
         for (int j = 0; j <= i; j++) {
             double s = A[i * n + j];
@@ -191,6 +191,10 @@ template <int NMAX> MP_HD bool cholesky_solve(int n, const double *A, const doub
     for (int i = 0; i < n; i++)
         if (!finite_d(x[i])) return false;
     return true;
+}
+template <int NMAX> MP_HD bool cholesky_solve(int n, const double *A, const double *b, double *x) {
+    double L[NMAX * NMAX], y[NMAX];
+    return cholesky_solve_ws(n, A, b, x, L, y);
 }
 
 } // namespace mp

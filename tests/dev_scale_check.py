@@ -15,6 +15,7 @@ for rep in range(int(os.environ.get("REPS", "3"))):
     t1 = time.time(); mg, sg, ig = ctx.estimate_batch(kind, pairs, opt, cfg); t2 = time.time()
     k, t, l = ctx.last_timing()
     print("gpu wall %.3fs kernel %.1f ms total %.1f ms launches %d -> %.0f pairs/s" % (t2 - t1, k, t, l, npairs / (t * 1e-3)))
+print("phase Mcycles", {k: round(v / 1e6, 1) for k, v in ctx.last_phase_cycles().items()})
 print("iters mean", np.mean([s.num_iterations_total for s in sg]), "lo mean", np.mean([s.number_lo_iterations for s in sg]),
       "hyps", sum(s.hypotheses_scored for s in sg), "evals %.3e" % sum(s.residual_evals for s in sg), "lm", sum(s.lm_solves for s in sg), sum(s.lm_iterations for s in sg))
 if check:

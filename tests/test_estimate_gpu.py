@@ -19,6 +19,8 @@ def rot_err_deg(Ra, Rb):
 
 
 def vec_angle_deg(a, b):
+    if not np.any(a) and not np.any(b):
+        return 0.0
     c = a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-300)
     return np.degrees(np.arccos(np.clip(c, -1, 1)))
 
