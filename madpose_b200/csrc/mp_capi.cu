@@ -99,6 +99,9 @@ void mp_destroy(mp_ctx *c) {
     cudaStreamSynchronize(c->stream);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     for (auto &e : c->tick_ev) cudaEventDestroy(e);
+    for (auto &e : c->gev) cudaEventDestroy(e);
+    for (auto &g : c->gstream) cudaStreamDestroy(g);
+    if (c->ev_init) cudaEventDestroy(c->ev_init);
     if (c->loop_alloc) delete static_cast<mp::LoopAlloc *>(c->loop_alloc);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;

@@ -2,6 +2,7 @@
 #include "mp_estimate.cuh"
 #include "mp_loop_kernels.cuh"
 #include <algorithm>
+#include <thread>
 
 namespace mp {
 
@@ -68,29 +69,43 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.inl_cur.reserve((3 * (size_t)N + 4) * sizeof(int)));
     MP_CUDA(A.flat.reserve(2 * (size_t)CAP * sizeof(int)));
     MP_CUDA(A.sample.reserve(3 * (size_t)CAP * sizeof(int)));
-    MP_CUDA(A.misc.reserve(256));
+    MP_CUDA(A.misc.reserve(1024));
     MP_CUDA(A.off3.reserve((n_pairs + 1) * sizeof(long long)));
     MP_CUDA(A.caps.reserve(n_pairs * sizeof(int)));
     MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.out_models.reserve(n_pairs * sizeof(mp_model)));
     MP_CUDA(A.out_stats.reserve(n_pairs * sizeof(mp_stats)));
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
-    MP_CUDA(A.h_active.reserve(64));
+    MP_CUDA(A.h_active.reserve(1024));
     LoopParams *prm = A.h_prm.as<LoopParams>();
     prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = LP_BMAX; prm->guard = 1e-3;
+    // groups of consecutive pairs, each driven on its own stream: a group's round waits only for
+    // its own slowest pair, and kernels of different groups overlap on the GPU
+    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 95) / 96;
+    G = std::max(1, std::min(G, c->groups_override > 0 ? 32 : 16));
+    const int gsz = (n_pairs + G - 1) / G;
+    G = (n_pairs + gsz - 1) / gsz;
     int *h_active = A.h_active.as<int>();
-    *h_active = n_pairs;
+    for (int g = 0; g < G; g++) h_active[g] = std::min(gsz, n_pairs - g * gsz);
+    while ((int)c->gstream.size() < G) {
+        cudaStream_t gs; cudaEvent_t ge;
+        MP_CUDA(cudaStreamCreateWithFlags(&gs, cudaStreamNonBlocking));
+        MP_CUDA(cudaEventCreateWithFlags(&ge, cudaEventDisableTiming));
+        c->gstream.push_back(gs); c->gev.push_back(ge);
+    }
+    if (!c->ev_init) MP_CUDA(cudaEventCreateWithFlags(&c->ev_init, cudaEventDisableTiming));
     MP_CUDA(cudaMemcpyAsync(A.prm.p, prm, sizeof(LoopParams), cudaMemcpyHostToDevice, s));
     MP_CUDA(cudaMemcpyAsync(A.off3.p, off3, (n_pairs + 1) * sizeof(long long), cudaMemcpyHostToDevice, s));
     MP_CUDA(cudaMemcpyAsync(A.caps.p, caps, n_pairs * sizeof(int), cudaMemcpyHostToDevice, s));
-    MP_CUDA(cudaMemcpyAsync(A.misc.p, h_active, sizeof(int), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(A.misc.as<char>() + 128, h_active, G * sizeof(int), cudaMemcpyHostToDevice, s));
     LoopBuffers L;
     L.pc = c->d_pc.as<PairConst>(); L.M = c->d_m64.as<Match64>(); L.S32 = c->d_s32.as<float4>();
     L.st = A.st.as<PairState>(); L.wk = A.wk.as<PairWork>(); L.rngA = A.rngA.as<MtStream>(); L.rngB = A.rngB.as<MtStream>();
     L.models = A.models.as<Model>(); L.hyps = A.hyps.as<HypF>();
     L.inl_best = A.inl_best.as<int>(); L.inl_cur = A.inl_cur.as<int>(); L.flat = A.flat.as<int>(); L.sample = A.sample.as<int>();
-    L.n_active = A.misc.as<int>();
-    L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>() + 64);
+    L.n_active = reinterpret_cast<int *>(A.misc.as<char>() + 128);
+    L.gsz = gsz;
+    L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>());
     MP_CUDA(cudaMemsetAsync(L.clk, 0, 64, s));
     const LoopParams *dprm = A.prm.as<LoopParams>();
     MP_CUDA(cudaEventRecord(c->ev[1], s));
@@ -115,26 +130,61 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         c->tick_cls[c->n_tick] = cls;
         return cudaEventRecord(c->tick_ev[c->n_tick++], s);
     };
-    while (true) {
-        MP_CUDA(cudaMemcpyAsync(h_active, A.misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
-        MP_CUDA(cudaStreamSynchronize(s));
-        if (*h_active <= 0) break;
-        if (++rounds > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
-        MP_CUDA(tick(0));
-        sample_kernel<<<(n_pairs + 31) / 32, 32, 0, s>>>(L, dprm);
-        MP_CUDA(tick(1));
-        MP_CUDA(launch_minimal_batch(L, dprm, n_pairs, s));
-        MP_CUDA(tick(2));
-        if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, n_pairs, tile_cap, smem, s));
-        else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, n_pairs, tile_cap, smem, s));
-        else MP_CUDA(launch_score_kind<TWO>(L, dprm, n_pairs, tile_cap, smem, s));
-        MP_CUDA(tick(3));
-        if (kind == CALIB) MP_CUDA(launch_decide_kind<CALIB>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
-        else if (kind == SHARED) MP_CUDA(launch_decide_kind<SHARED>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
-        else MP_CUDA(launch_decide_kind<TWO>(L, dprm, n_pairs, A.off3.as<long long>(), A.caps.as<int>(), s));
-        MP_CUDA(tick(-1));
-        launches += 4;
+    MP_CUDA(cudaEventRecord(c->ev_init, s));
+    std::vector<int> act(G), pending(G, 0);
+    std::vector<long long> grounds(G, 0);
+    for (int g = 0; g < G; g++) {
+        act[g] = h_active[g];
+        if (G > 1) MP_CUDA(cudaStreamWaitEvent(c->gstream[g], c->ev_init, 0));
     }
+    auto enqueue_round = [&](int g) -> int {
+        cudaStream_t gs = G > 1 ? c->gstream[g] : s;
+        const int first = g * gsz, count = std::min(gsz, n_pairs - first);
+        const bool timed = G == 1;
+        if (timed) MP_CUDA(tick(0));
+        sample_kernel<<<(count + 31) / 32, 32, 0, gs>>>(L, dprm, first, count);
+        if (timed) MP_CUDA(tick(1));
+        MP_CUDA(launch_minimal_batch(L, dprm, first, count, gs));
+        if (timed) MP_CUDA(tick(2));
+        if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, first, count, tile_cap, smem, gs));
+        else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, first, count, tile_cap, smem, gs));
+        else MP_CUDA(launch_score_kind<TWO>(L, dprm, first, count, tile_cap, smem, gs));
+        if (timed) MP_CUDA(tick(3));
+        if (kind == CALIB) MP_CUDA(launch_decide_kind<CALIB>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
+        else if (kind == SHARED) MP_CUDA(launch_decide_kind<SHARED>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
+        else MP_CUDA(launch_decide_kind<TWO>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
+        if (timed) MP_CUDA(tick(-1));
+        MP_CUDA(cudaMemcpyAsync(h_active + g, L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, gs));
+        MP_CUDA(cudaEventRecord(c->gev[g], gs));
+        launches += 4;
+        return MP_OK;
+    };
+    while (true) {
+        bool any = false, progress = false;
+        for (int g = 0; g < G; g++) {
+            if (act[g] <= 0 && !pending[g]) continue;
+            any = true;
+            if (pending[g]) {
+                cudaError_t q = cudaEventQuery(c->gev[g]);
+                if (q == cudaErrorNotReady) continue;
+                MP_CUDA(q);
+                pending[g] = 0;
+                act[g] = h_active[g];
+                progress = true;
+                if (act[g] <= 0) continue;
+            }
+            if (++grounds[g] > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
+            int rc2 = enqueue_round(g);
+            if (rc2) return rc2;
+            pending[g] = 1;
+            progress = true;
+        }
+        if (!any) break;
+        if (!progress) std::this_thread::yield();
+    }
+    for (int g = 0; g < G; g++) rounds = std::max(rounds, grounds[g]);
+    if (G > 1)
+        for (int g = 0; g < G; g++) MP_CUDA(cudaStreamWaitEvent(s, c->gev[g], 0));
     finalize_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, n_pairs, A.out_models.as<mp_model>(), A.out_stats.as<mp_stats>());
     MP_CUDA(cudaGetLastError());
     launches += 1;
@@ -142,6 +192,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaMemcpyAsync(out_models, A.out_models.p, n_pairs * sizeof(mp_model), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(out_stats, A.out_stats.p, n_pairs * sizeof(mp_stats), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(c->phase_clk, L.clk, 64, cudaMemcpyDeviceToHost, s));
+    c->last_groups = G;
     if (out_inliers && N > 0)
         MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, 3 * (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaEventRecord(c->ev[3], s));
@@ -241,6 +292,12 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
     if (rc) return rc;
     c->resident_kind = kind; c->resident_pairs = n_pairs;
     return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, false);
+}
+int mp_set_groups(mp_ctx *c, int groups) {
+    using namespace mp;
+    if (!c || groups < 0 || groups > 32) return fail(MP_ERR_ARG, "mp_set_groups: 0 (automatic) .. 32");
+    c->groups_override = groups;
+    return MP_OK;
 }
 int mp_last_phase_cycles(mp_ctx *c, unsigned long long *cycles8) {
     using namespace mp;

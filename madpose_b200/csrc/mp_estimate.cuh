@@ -5,12 +5,12 @@
 
 namespace mp {
 
-cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int n_pairs, cudaStream_t s);
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, cudaStream_t s);
 template <int KIND>
-cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, int tile_cap, size_t smem, cudaStream_t s);
+cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, int tile_cap, size_t smem, cudaStream_t s);
 template <int KIND>
-cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, const long long *off3, const int *caps,
-                               cudaStream_t s);
+cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
+                               const int *caps, cudaStream_t s);
 template <int KIND>
 cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopParams *dprm, int n_problems, const Model *start,
                            const int *idx, const int *off, Model *out, double *info, cudaStream_t s);

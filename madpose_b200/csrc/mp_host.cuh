@@ -75,6 +75,10 @@ struct mp_ctx {
     unsigned long long phase_clk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
+    int groups_override = 0, last_groups = 1; // 0 = automatic
+    std::vector<cudaStream_t> gstream;
+    std::vector<cudaEvent_t> gev;
+    cudaEvent_t ev_init = nullptr;
     void *loop_alloc = nullptr; // mp::LoopAlloc, created on first mp_estimate_batch
     uint32_t tape_seed = 0;
     size_t tape_len = 0;

@@ -8,13 +8,13 @@ namespace mp {
 
 // ---- K3 over all hypotheses of the round: one CTA per pair, tile staged once (bulk copy)
 template <int KIND>
-__global__ void __launch_bounds__(MP_CTA, 1) score_batch_kernel(LoopBuffers L, const LoopParams *prmp, int tile_cap) {
+__global__ void __launch_bounds__(MP_CTA, 1) score_batch_kernel(LoopBuffers L, const LoopParams *prmp, int tile_cap, int first) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t bar;
     __shared__ unsigned short list[LP_BMAX * LP_MM];
     __shared__ int nlist;
     const LoopParams &prm = *prmp;
-    const int p = blockIdx.x;
+    const int p = first + blockIdx.x;
     const PairState &S = L.st[p];
     if (S.phase != PH_ITER || S.batch_len == 0) return;
     const PairConst &pc = L.pc[p];
@@ -70,12 +70,12 @@ template <int KIND> __device__ void block_update_termination(const BlockCtx &C, 
 }
 
 template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) decide_kernel(LoopBuffers L, const LoopParams *prmp,
-                                                                                  const long long *off3, const int *caps) {
+                                                                                  const long long *off3, const int *caps, int first) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     __shared__ double lo_score;
     const LoopParams &prm = *prmp;
-    const int p = blockIdx.x;
+    const int p = first + blockIdx.x;
     if (L.st[p].phase == PH_DONE) return;
     {
         const int *src = reinterpret_cast<const int *>(&L.st[p]);
@@ -225,23 +225,23 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
         for (int i = threadIdx.x; i < (int)(sizeof(PairState) / 4); i += blockDim.x) dst[i] = src[i];
     }
     if (threadIdx.x == 0 && S.phase == PH_DONE) {
-        atomicSub(L.n_active, 1);
+        atomicSub(L.n_active + p / L.gsz, 1);
         for (int q = 0; q < 8; q++) atomicAdd(L.clk + q, S.clk[q]);
     }
 }
 
 
 template <int KIND>
-cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, int tile_cap, size_t smem, cudaStream_t s) {
+cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, int tile_cap, size_t smem, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(score_batch_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    score_batch_kernel<KIND><<<n_pairs, MP_CTA, smem, s>>>(L, dprm, tile_cap);
+    score_batch_kernel<KIND><<<count, MP_CTA, smem, s>>>(L, dprm, tile_cap, first);
     return cudaGetLastError();
 }
 template <int KIND>
-cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int n_pairs, const long long *off3, const int *caps,
-                               cudaStream_t s) {
-    decide_kernel<KIND><<<n_pairs, LP_THREADS, 0, s>>>(L, dprm, off3, caps);
+cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
+                               const int *caps, cudaStream_t s) {
+    decide_kernel<KIND><<<count, LP_THREADS, 0, s>>>(L, dprm, off3, caps, first);
     return cudaGetLastError();
 }
 

@@ -1,7 +1,7 @@
 // explicit instantiation of the per-kind loop kernels (kind 2); see mp_kind.cuh
 #include "mp_kind.cuh"
 namespace mp {
-template cudaError_t launch_score_kind<2>(LoopBuffers, const LoopParams *, int, int, size_t, cudaStream_t);
-template cudaError_t launch_decide_kind<2>(LoopBuffers, const LoopParams *, int, const long long *, const int *, cudaStream_t);
+template cudaError_t launch_score_kind<2>(LoopBuffers, const LoopParams *, int, int, int, size_t, cudaStream_t);
+template cudaError_t launch_decide_kind<2>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, cudaStream_t);
 template cudaError_t launch_lm_kind<2>(const PairConst *, const Match64 *, const LoopParams *, int, const Model *, const int *, const int *, Model *, double *, cudaStream_t);
 }

@@ -75,7 +75,8 @@ struct LoopBuffers {
     int *inl_cur;   // [3 * off] scratch: inliers of the model being refined
     int *flat;      // [3 * off + pad] scratch: flattened inlier list / shuffled sample
     int *sample;    // [3 * off + pad] scratch: un-flattened sample lists
-    int *n_active;  // device counter of pairs not yet PH_DONE
+    int *n_active;  // device counters of pairs not yet PH_DONE, one per group of gsz consecutive pairs
+    int gsz;
     unsigned long long *clk; // [8] phase cycle totals over all pairs (profiling aid)
 };
 

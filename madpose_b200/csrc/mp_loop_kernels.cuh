@@ -40,15 +40,15 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
     for (int q = 0; q < 8; q++) S.clk[q] = 0;
     mt_seed(&L.rngA[p], prm.opt.random_seed);
     mt_seed(&L.rngB[p], prm.opt.random_seed);
-    if (S.phase == PH_DONE) atomicSub(L.n_active, 1);
+    if (S.phase == PH_DONE) atomicSub(L.n_active + p / L.gsz, 1);
 }
 
 // ---- SelectMinimalSolver (hybrid_ransac.h:210-243) + HybridUniformSampling::Sample for the
 // next iterations of every iterating pair; one thread per pair
-__global__ void sample_kernel(LoopBuffers L, const LoopParams *prmp) {
+__global__ void sample_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= prm.n_pairs) return;
+    const int q = blockIdx.x * blockDim.x + threadIdx.x, p = first + q;
+    if (q >= count) return;
     PairState &S = L.st[p];
     if (S.phase != PH_ITER) { S.batch_len = 0; return; }
     PairWork &W = L.wk[p];

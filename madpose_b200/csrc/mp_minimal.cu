@@ -26,11 +26,11 @@ __global__ void __launch_bounds__(64) minimal_kernel(const PairConst *pcp, const
 }
 
 // ---- K1/K2 over all samples of the round: one thread per (pair, iteration)
-__global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp) {
+__global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    const int p = g / LP_BMAX, b = g % LP_BMAX;
-    if (p >= prm.n_pairs) return;
+    const int p = first + g / LP_BMAX, b = g % LP_BMAX;
+    if (g / LP_BMAX >= count) return;
     const PairState &S = L.st[p];
     if (S.phase != PH_ITER || b >= S.batch_len) return;
     const PairConst &pc = L.pc[p];
@@ -44,8 +44,8 @@ __global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const 
 }
 
 
-cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int n_pairs, cudaStream_t s) {
-    minimal_batch_kernel<<<(n_pairs * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm);
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, cudaStream_t s) {
+    minimal_batch_kernel<<<(count * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
     return cudaGetLastError();
 }
 

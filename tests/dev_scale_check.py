@@ -6,6 +6,7 @@ from madpose_b200 import capi
 config = int(sys.argv[1]); npairs = int(sys.argv[2]); check = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 ora = oracle_lib.load(build=False)
 ctx = capi.Context(0)
+ctx.set_groups(int(os.environ.get('MP_GROUPS', '0')))
 t0 = time.time()
 ps = [problem(config, p=i) for i in range(npairs)]
 print("gen %.1fs" % (time.time() - t0))
