@@ -171,6 +171,7 @@ def main():
     ctx.estimate_resident(opt, cfg)
     brk, _ = ctx.last_breakdown()
     single_stream_ms = ctx.last_timing()[1]
+    phase_cycles = ctx.last_phase_cycles()
     ctx.set_groups(0)
     sampler.stop_flag = True; sampler.join()
 
@@ -213,6 +214,7 @@ def main():
             "gpu_launches": int(launches),
             "rounds_per_step": rounds / a.steps,
             "kernel_ms_per_step_single_stream": share, "single_stream_ms_per_step": single_stream_ms,
+            "decide_phase_gcycles": {k2: round(v / 1e9, 3) for k2, v in phase_cycles.items()},
             "roofline": {"bound": bound, "kernel": dom, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach / peak, "traffic": None,
                          "peak_source": "register-only FFMA / DFMA probes measured in this run (fp32 %.1f, fp64 %.1f TFLOP/s); "

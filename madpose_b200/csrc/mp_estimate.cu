@@ -142,7 +142,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         const int first = g * gsz, count = std::min(gsz, n_pairs - first);
         const bool timed = G == 1;
         if (timed) MP_CUDA(tick(0));
-        sample_kernel<<<(count + 31) / 32, 32, 0, gs>>>(L, dprm, first, count);
+        sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
         if (timed) MP_CUDA(tick(1));
         MP_CUDA(launch_minimal_batch(L, dprm, first, count, gs));
         if (timed) MP_CUDA(tick(2));

@@ -231,3 +231,6 @@ template <int KIND> MP_HD void lm_block(const PairConst &pc, const Match64 &m, i
 
 } // namespace mp
 #include "mp_lm2.cuh"
+#ifdef __CUDACC__
+#include "mp_lm_warp.cuh"
+#endif

@@ -1,0 +1,237 @@
+// K5 (part 3) -- the LM driver of mp_lm2.cuh executed by ONE WARP instead of one thread.
+// Same state (an LmDriver in shared memory), same arithmetic per element and the same order of
+// every floating-point sum as the scalar driver (so both produce identical bits); what changes
+// is who does it: the 11 x 11 systems are spread over the lanes (lane = row), the Cholesky
+// factorisation is right-looking with the rows in registers and the pivot column broadcast by
+// shuffles, the forward substitution is column-oriented.  Scalar decisions are taken by lane 0
+// and broadcast.  All 32 lanes of the warp must call these functions together.
+#pragma once
+
+namespace mp {
+
+constexpr unsigned LMW_FULL = 0xffffffffu;
+constexpr int LM_TRI = LM_NT * (LM_NT + 1) / 2;
+
+// reduced full-slot sums (LmAcc as a flat array) -> compact nt x nt system; = lm_compress
+__device__ __forceinline__ void warp_compress(const LmSetup &L, const double *tot, double *A, double *g, int lane) {
+    const int nt = L.nt;
+    for (int k = lane; k < LM_TRI; k += 32) {
+        int a = 0, r = k;
+        while (r >= LM_NT - a) { r -= LM_NT - a; a++; }
+        const int b = a + r, ia = L.slot[a], ib = L.slot[b];
+        if (ia >= 0 && ib >= 0) {
+            const double v = tot[k];
+            A[ia * nt + ib] = v; A[ib * nt + ia] = v;
+        }
+    }
+    if (lane < LM_NT && L.slot[lane] >= 0) g[L.slot[lane]] = tot[LM_TRI + lane];
+    __syncwarp();
+}
+
+// LmDriver::first
+__device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
+    const LmSetup &L = *d.L;
+    const int nt = L.nt;
+    warp_compress(L, tot, d.A, d.g, lane);
+    if (lane < nt) d.scale[lane] = 1.0 / (1.0 + sqrt(d.A[lane * nt + lane]));
+    __syncwarp();
+    int go = 0;
+    if (lane == 0) {
+        d.cost = tot[LM_TRI + LM_NT];
+        d.info.cost0 = d.cost; d.info.cost = d.cost;
+        if (!finite_d(d.cost)) d.info.termination = 3;
+        else if (d.grad_max(d.x, d.g) <= L.gtol) d.info.termination = 1;
+        else {
+            d.radius = 1e4; d.decrease = 2.0;
+            d.min_cost = d.cur_cost = d.ref_cost = d.cand_cost = d.cost; d.acc_ref = 0; d.acc_cand = 0;
+            d.n_nonmono = 0; d.n_invalid = 0; d.it = 0;
+            d.info.termination = 2;
+            go = 1;
+        }
+    }
+    go = __shfl_sync(LMW_FULL, go, 0);
+    __syncwarp();
+    return go != 0;
+}
+
+// LmDriver::propose
+__device__ inline bool warp_lm_propose(LmDriver &d, int lane) {
+    const LmSetup &L = *d.L;
+    const int nt = L.nt;
+    while (true) {
+        int stop = 0;
+        if (lane == 0) {
+            if (++d.it > L.max_it) { d.info.cost = d.cost; stop = 1; }
+            else {
+                d.info.iterations = d.it;
+                if (d.radius < 1e-32) { d.info.termination = 1; d.info.cost = d.cost; stop = 1; }
+            }
+        }
+        stop = __shfl_sync(LMW_FULL, stop, 0);
+        if (stop) return false;
+        __syncwarp();
+        const double radius = d.radius;
+        const bool rowl = lane < nt;
+        // my row of the scaled system; the damped copy stays in registers
+        double row[LM_NT];
+        const double sa = rowl ? d.scale[lane] : 0.0;
+#pragma unroll
+        for (int b = 0; b < LM_NT; b++) {
+            double v = 0.0;
+            if (rowl && b < nt) {
+                v = d.A[lane * nt + b] * sa * d.scale[b];
+                d.As[lane * nt + b] = v;
+            }
+            row[b] = v;
+        }
+        if (rowl) d.gs[lane] = d.g[lane] * sa;
+        {
+            double diag = 0.0;
+#pragma unroll
+            for (int b = 0; b < LM_NT; b++)
+                if (b == lane) diag = row[b];
+            const double add = fmin(fmax(diag, 1e-6), 1e32) / radius;
+#pragma unroll
+            for (int b = 0; b < LM_NT; b++)
+                if (b == lane) row[b] += add;
+        }
+        __syncwarp();
+        // right-looking Cholesky: after step k, row[k] = L[lane][k]
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < LM_NT; k++) {
+            if (k < nt && ok) {
+                const double dk = __shfl_sync(LMW_FULL, row[k], k);
+                if (!(dk > 0.0) || !finite_d(dk)) ok = false;
+                else {
+                    const double lkk = sqrt(dk);
+                    const double lik = lane == k ? lkk : row[k] / lkk;
+                    row[k] = lik;
+#pragma unroll
+                    for (int j = k + 1; j < LM_NT; j++) {
+                        const double ljk = __shfl_sync(LMW_FULL, lik, j);
+                        if (j < nt && j <= lane) row[j] -= lik * ljk;
+                    }
+                }
+            }
+        }
+        double xs[LM_NT];
+        if (ok) {
+            if (rowl) {
+#pragma unroll
+                for (int j = 0; j < LM_NT; j++)
+                    if (j <= lane) d.Lc[lane * nt + j] = row[j];
+            }
+            // forward substitution, column-oriented: y_k known -> every later row subtracts L[i][k] y_k
+            double s = rowl ? d.gs[lane] : 0.0;
+#pragma unroll
+            for (int k = 0; k < LM_NT; k++) {
+                if (k < nt) {
+                    const double yk = __shfl_sync(LMW_FULL, s / row[k], k);
+                    if (lane == k) d.yw[k] = yk;
+                    if (lane > k) s -= row[k] * yk;
+                }
+            }
+            __syncwarp();
+            // back substitution (every lane, redundantly; sums in the scalar order k = i+1 .. nt-1)
+#pragma unroll
+            for (int i = LM_NT - 1; i >= 0; i--) {
+                double v = 0.0;
+                if (i < nt) {
+                    double t = d.yw[i];
+#pragma unroll
+                    for (int k = i + 1; k < LM_NT; k++)
+                        if (k < nt) t -= d.Lc[k * nt + i] * xs[k];
+                    v = t / d.Lc[i * nt + i];
+                    if (!finite_d(v)) ok = false;
+                }
+                xs[i] = v;
+            }
+        }
+        double mcc = 0;
+        if (ok) {
+            double dg = 0, dAd = 0;
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++) xs[a] = -xs[a];
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++) {
+                if (a < nt) {
+                    dg += xs[a] * d.gs[a];
+#pragma unroll
+                    for (int b = 0; b < LM_NT; b++)
+                        if (b < nt) dAd += xs[a] * d.As[a * nt + b] * xs[b];
+                }
+            }
+            mcc = -(dg + 0.5 * dAd);
+        }
+        if (!ok || !(mcc > 0)) {
+            int fail_ = 0;
+            if (lane == 0) {
+                if (++d.n_invalid >= 5) { d.info.termination = 3; d.info.cost = d.cost; fail_ = 1; }
+                else { d.radius /= d.decrease; d.decrease *= 2; }
+            }
+            fail_ = __shfl_sync(LMW_FULL, fail_, 0);
+            if (fail_) return false;
+            __syncwarp();
+            continue;
+        }
+        if (lane == 0) {
+            d.mcc = mcc;
+            d.n_invalid = 0;
+            double dd[LM_NT];
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++) {
+                dd[a] = a < nt ? xs[a] * d.scale[a] : 0.0;
+                if (a < nt) d.y[a] = xs[a];
+            }
+            lm_plus(L, d.x, dd, d.xc);
+        }
+        __syncwarp();
+        return true;
+    }
+}
+
+// LmDriver::feed
+__device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
+    const LmSetup &L = *d.L;
+    const int nt = L.nt;
+    warp_compress(L, tot, d.An, d.gn, lane);
+    int verdict = 0; // 0 finished, 1 rejected step (continue), 2 accepted step
+    double cc = 0, rel = 0;
+    if (lane == 0) {
+        cc = tot[LM_TRI + LM_NT];
+        if (!finite_d(cc)) cc = DBL_MAX;
+        double sn = 0, xn = 0;
+        for (int k = 0; k < LM_NA; k++) { sn += (d.xc[k] - d.x[k]) * (d.xc[k] - d.x[k]); xn += d.x[k] * d.x[k]; }
+        if (sqrt(sn) <= L.ptol * (sqrt(xn) + L.ptol)) { d.info.termination = 1; d.info.cost = d.cost; }
+        else if (fabs(d.cost - cc) <= L.ftol * d.cost) { d.info.termination = 1; d.info.cost = d.cost; }
+        else {
+            rel = cc >= DBL_MAX ? -DBL_MAX : fmax((d.cur_cost - cc) / d.mcc, (d.ref_cost - cc) / (d.acc_ref + d.mcc));
+            if (rel > 1e-3) verdict = 2;
+            else { d.radius /= d.decrease; d.decrease *= 2; verdict = 1; }
+        }
+    }
+    verdict = __shfl_sync(LMW_FULL, verdict, 0);
+    if (verdict == 2) {
+        for (int e = lane; e < nt * nt; e += 32) d.A[e] = d.An[e];
+        if (lane < nt) d.g[lane] = d.gn[lane];
+        __syncwarp();
+        if (lane == 0) {
+            for (int k = 0; k < LM_NA; k++) d.x[k] = d.xc[k];
+            d.cost = cc;
+            const double tt = 2.0 * rel - 1.0;
+            d.radius = fmin(1e16, d.radius / fmax(1.0 / 3.0, 1.0 - tt * tt * tt));
+            d.decrease = 2.0;
+            d.cur_cost = cc; d.acc_cand += d.mcc; d.acc_ref += d.mcc;
+            if (d.cur_cost < d.min_cost) { d.min_cost = d.cur_cost; d.n_nonmono = 0; d.cand_cost = d.cur_cost; d.acc_cand = 0; }
+            else { ++d.n_nonmono; if (d.cur_cost > d.cand_cost) { d.cand_cost = d.cur_cost; d.acc_cand = 0; } }
+            if (d.n_nonmono == L.max_nonmono) { d.ref_cost = d.cand_cost; d.acc_ref = d.acc_cand; }
+            if (d.grad_max(d.x, d.g) <= L.gtol) { d.info.termination = 1; d.info.cost = d.cost; verdict = 0; }
+        }
+        verdict = __shfl_sync(LMW_FULL, verdict, 0);
+    }
+    __syncwarp();
+    return verdict != 0;
+}
+
+} // namespace mp

@@ -44,13 +44,34 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
 }
 
 // ---- SelectMinimalSolver (hybrid_ransac.h:210-243) + HybridUniformSampling::Sample for the
-// next iterations of every iterating pair; one thread per pair
-__global__ void sample_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+// next iterations of every iterating pair.  One WARP per pair: the lanes extend the two
+// generator rings far enough for the whole batch and copy the raw words the batch can
+// consume into shared-memory windows; lane 0 then draws sequentially from the windows
+// (the draws of one stream are inherently sequential: rejection sampling).
+constexpr int SMP_WARPS = 4, SMP_WIN_A = 640, SMP_WIN_B = 96;
+
+__device__ inline void warp_fill_window(MtStream *g, uint32_t *win, int need, int lane) {
+    while (g->gen < g->pos + (unsigned long long)need) mt_refill(g, lane, 32, [] { __syncwarp(); });
+    const unsigned base = (unsigned)(g->pos % MT_RING);
+    for (int i = lane; i < need; i += 32) {
+        unsigned r = base + (unsigned)i;
+        if (r >= (unsigned)MT_RING) r -= MT_RING;
+        win[i] = g->x[r];
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    __shared__ uint32_t winA[SMP_WARPS][SMP_WIN_A], winB[SMP_WARPS][SMP_WIN_B];
     const LoopParams &prm = *prmp;
-    const int q = blockIdx.x * blockDim.x + threadIdx.x, p = first + q;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * SMP_WARPS + warp, p = first + q;
     if (q >= count) return;
     PairState &S = L.st[p];
-    if (S.phase != PH_ITER) { S.batch_len = 0; return; }
+    if (S.phase != PH_ITER) {
+        if (lane == 0) S.batch_len = 0;
+        return;
+    }
     PairWork &W = L.wk[p];
     MtStream *A = &L.rngA[p], *B = &L.rngB[p];
     const int n = L.pc[p].n;
@@ -59,27 +80,37 @@ __global__ void sample_kernel(LoopBuffers L, const LoopParams *prmp, int first, 
     const unsigned lo_start = prm.opt.lo_starting_iterations;
     unsigned len = (unsigned)S.B < max_it - S.it ? (unsigned)S.B : max_it - S.it;
     if (S.it < lo_start && len > lo_start - S.it) len = lo_start - S.it; // a batch never straddles lo_start
+    warp_fill_window(A, winA[warp], SMP_WIN_A, lane);
+    warp_fill_window(B, winB[warp], SMP_WIN_B, lane);
+    if (lane != 0) return;
+    MtWindow sa{A, winA[warp], A->pos, SMP_WIN_A, 0, false}, sb{B, winB[warp], B->pos, SMP_WIN_B, 0, false};
+    const double prior0 = S.prior[0], prior1 = S.prior[1];
+    int sizes[2][3];
+    for (int s = 0; s < 2; s++)
+        for (int t = 0; t < 3; t++) sizes[s][t] = S.sizes[s][t];
     for (unsigned b = 0; b < len; b++) {
-        const double u = mt_uniform_real(B, S.prior[0] + S.prior[1]);
+        const double u = mt_uniform_real_t(sb, prior0 + prior1);
         int s = -1;
         double c = 0;
         for (int k = 0; k < 2; k++) {
-            if (S.prior[k] == 0.0) continue;
-            c += S.prior[k];
+            const double pk = k == 0 ? prior0 : prior1;
+            if (pk == 0.0) continue;
+            c += pk;
             if (u <= c) { s = k; break; }
         }
-        if (s < 0) s = S.prior[1] > 0.0 ? 1 : 0; // unreachable (u <= sum of priors)
+        if (s < 0) s = prior1 > 0.0 ? 1 : 0; // unreachable (u <= sum of priors)
         int tmp[8], scratch[16];
         for (int t = 0; t < 3; t++) {
-            const int k = S.sizes[s][t];
+            const int k = sizes[s][t];
             if (k <= 0) continue;
-            mt_draw_sample(A, n, k, tmp, scratch); // type 1 of solver 0 is drawn and discarded (quirk Q1)
+            mt_draw_sample_t(sa, n, k, tmp, scratch); // type 1 of solver 0 is drawn and discarded (quirk Q1)
             if ((s == 0 && t == 0) || (s == 1 && t == 2))
                 for (int i = 0; i < k; i++) W.idx[b][i] = tmp[i];
         }
         W.solver[b] = s;
-        W.posA[b] = A->pos; W.posB[b] = B->pos;
+        W.posA[b] = sa.position(); W.posB[b] = sb.position();
     }
+    A->pos = sa.position(); B->pos = sb.position();
     S.batch_len = (int)len;
 }
 

@@ -82,7 +82,7 @@ template <int KIND> struct BlockEval {
 };
 static_assert(sizeof(LmAcc) == LM_ACC_DOUBLES * sizeof(double), "LmAcc is a flat array of doubles");
 
-// One LM solve by the CTA: thread 0 runs the driver (LmDriver), everybody evaluates.
+// One LM solve by the CTA: warp 0 runs the driver (LmDriver state, mp_lm_warp.cuh), everybody evaluates.
 // x0 -> x (final parameters, valid on thread 0 only); returns info on thread 0.
 template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L, const BlockEval<KIND> &ev,
                                              const Model &start, Model *out, LmInfo *info_out) {
@@ -98,19 +98,20 @@ template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L
     }
     __syncthreads();
     if (sh->lm_go) {
+        const int lane = threadIdx.x & 31;
         ev();
-        if (threadIdx.x == 0) {
-            const bool go = drv.first(*reinterpret_cast<const LmAcc *>(sh->total)) && drv.propose();
-            sh->lm_go = go ? 1 : 0;
-            for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.xc[k];
+        if (threadIdx.x < 32) { // warp 0 drives (mp_lm_warp.cuh); the other warps wait at the barrier
+            const bool go = warp_lm_first(drv, sh->total, lane) && warp_lm_propose(drv, lane);
+            if (lane == 0) sh->lm_go = go ? 1 : 0;
+            if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
         }
         __syncthreads();
         while (sh->lm_go) {
             ev();
-            if (threadIdx.x == 0) {
-                const bool go = drv.feed(*reinterpret_cast<const LmAcc *>(sh->total)) && drv.propose();
-                sh->lm_go = go ? 1 : 0;
-                for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.xc[k];
+            if (threadIdx.x < 32) {
+                const bool go = warp_lm_feed(drv, sh->total, lane) && warp_lm_propose(drv, lane);
+                if (lane == 0) sh->lm_go = go ? 1 : 0;
+                if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
             }
             __syncthreads();
         }
@@ -147,8 +148,8 @@ template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, 
 //  (1) ALL n-1 draws are evaluated in parallel straight from the generator ring (draw i uses
 //      word pos+i unless an earlier draw hit a Lemire rejection, which is detected in parallel
 //      and resolved sequentially for that one draw);
-//  (2) the first head = min(target, n-1) swaps are replayed by one thread on shared memory
-//      only: prefetched original values + a small hash table of displaced positions.
+//  (2) the first head = min(target, n-1) swaps are replayed in parallel from prefetched
+//      original values (see "Parallel replay" below).
 __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *v, int *len_sh) {
     MP_CLK_BEGIN();
     MtStream *g = C.rngB;
@@ -157,7 +158,7 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
     const int n = *len_sh;
     __syncthreads();
     const int head = n - 1 < target ? (n - 1 > 0 ? n - 1 : 0) : target;
-    const bool fast = head <= SH_MAXHEAD;
+    const bool fast = head <= SH_MAXHEAD && n < (1 << 21);
     if (!fast) {
         if (threadIdx.x == 0)
             for (int i = 0; i < head; i++) {
@@ -165,8 +166,6 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
                 const int t = v[i]; v[i] = v[j]; v[j] = t;
             }
         __syncthreads();
-    } else {
-        for (int k = threadIdx.x; k < SH_TAB; k += blockDim.x) sh->sh_key[k] = -1;
     }
     int i = fast ? 0 : head; // draws still to take: uniform_int(i, n-1) for i in [i, n-1)
     while (i < n - 1) {
@@ -174,8 +173,10 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
         const unsigned long long pos = g->pos;
         const int avail = (int)(g->gen - pos), m = avail < n - 1 - i ? avail : n - 1 - i;
         int first = m;
+        const unsigned rbase = (unsigned)(pos % MT_RING); // m <= 624 < MT_RING: one conditional wrap per index
+        auto ring_at = [&](int j) { const unsigned r = rbase + (unsigned)j; return g->x[r >= (unsigned)MT_RING ? r - MT_RING : r]; };
         for (int j = threadIdx.x; j < m; j += blockDim.x) {
-            const uint32_t w = mt_temper(g->x[(pos + j) % MT_RING]);
+            const uint32_t w = mt_temper(ring_at(j));
             if (mt_lemire_rejects(w, (uint32_t)(n - (i + j)))) { first = j; break; }
         }
         __syncthreads();
@@ -186,7 +187,7 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
         first = sh->flag[0];
         if (fast) // draws [i, i+first) are valid: record those of the head
             for (int j = threadIdx.x; j < first && i + j < head; j += blockDim.x) {
-                const uint32_t w = mt_temper(g->x[(pos + j) % MT_RING]);
+                const uint32_t w = mt_temper(ring_at(j));
                 const int ii = i + j, jj = ii + (int)(((unsigned long long)w * (uint32_t)(n - ii)) >> 32);
                 sh->sh_j[ii] = jj; sh->sh_vi[ii] = v[ii]; sh->sh_vj[ii] = v[jj];
             }
@@ -201,27 +202,59 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
         i += first + (first < m ? 1 : 0);
         __syncthreads();
     }
-    if (fast && threadIdx.x == 0) {
-        auto slot = [&](int key) { // open addressing, linear probing; returns the slot holding key or the free one
-            unsigned h = ((unsigned)key * 2654435761u) >> 21;
-            while (sh->sh_key[h] != -1 && sh->sh_key[h] != key) h = (h + 1) & (SH_TAB - 1);
-            return (int)h;
-        };
-        for (int k = 0; k < head; k++) {
-            const int j = sh->sh_j[k];
-            int h = slot(k);
-            const int a = sh->sh_key[h] == k ? sh->sh_val[h] : sh->sh_vi[k];
-            int b = a;
-            if (j != k) {
-                h = slot(j);
-                b = sh->sh_key[h] == j ? sh->sh_val[h] : sh->sh_vj[k];
-                sh->sh_key[h] = j; sh->sh_val[h] = a;
+    if (fast && head > 0) {
+        // Parallel replay.  Swap i exchanges positions i and j_i >= i, so position k < head is final after
+        // step k and holds the value that sat at position j_k just before step k:
+        //   a(i)   = value at position i just before step i = a(i') for the latest i' < i with j_i' == i, else v0[i]
+        //   out[k] = a(k) if j_k == k, else a(q) for the latest q < k with j_q == j_k, else v0[j_k]
+        // "latest earlier swap with the same target" = the predecessor in the list of swaps sorted by
+        // (target, time): bitonic sort of the keys (j_i << 10 | i) in shared memory.
+        int P = 1;
+        while (P < head) P <<= 1;
+        unsigned *key = reinterpret_cast<unsigned *>(sh->sh_key);
+        int *ps = sh->sh_val, *pt = sh->sh_val + SH_MAXHEAD;
+        for (int k = threadIdx.x; k < P; k += blockDim.x)
+            key[k] = k < head ? ((unsigned)sh->sh_j[k] << 10) | (unsigned)k : 0xffffffffu;
+        __syncthreads();
+        for (int kk = 2; kk <= P; kk <<= 1)
+            for (int jj = kk >> 1; jj > 0; jj >>= 1) {
+                for (int t = threadIdx.x; t < P / 2; t += blockDim.x) {
+                    const int lo = ((t & ~(jj - 1)) << 1) | (t & (jj - 1)), hi = lo | jj;
+                    const unsigned x = key[lo], y = key[hi];
+                    const bool up = (lo & kk) == 0;
+                    if ((x > y) == up) { key[lo] = y; key[hi] = x; }
+                }
+                __syncthreads();
             }
-            v[k] = b;
+        auto lower_bound = [&](unsigned want) { // first sorted position with key >= want
+            int lo = 0, hi = head;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (key[mid] < want) lo = mid + 1; else hi = mid;
+            }
+            return lo;
+        };
+        for (int s2 = threadIdx.x; s2 < head; s2 += blockDim.x) {
+            const unsigned kq = key[s2];
+            ps[kq & 1023u] = (s2 > 0 && (key[s2 - 1] >> 10) == (kq >> 10)) ? (int)(key[s2 - 1] & 1023u) : -1;
+            const int u = lower_bound(((unsigned)s2 << 10) | (unsigned)s2) - 1; // here s2 plays the role of position i
+            pt[s2] = (u >= 0 && (key[u] >> 10) == (unsigned)s2) ? (int)(key[u] & 1023u) : -1;
         }
-        if (head == n - 1 && n - 1 < target && n >= 1) { // the list grows: its last element is kept too
-            const int h = slot(n - 1);
-            if (sh->sh_key[h] == n - 1) v[n - 1] = sh->sh_val[h];
+        __syncthreads();
+        auto a_of = [&](int c) {
+            while (pt[c] >= 0) c = pt[c];
+            return sh->sh_vi[c];
+        };
+        for (int k = threadIdx.x; k < head; k += blockDim.x) {
+            const int j = sh->sh_j[k];
+            int out;
+            if (j == k) out = a_of(k);
+            else { const int q = ps[k]; out = q >= 0 ? a_of(q) : sh->sh_vj[k]; }
+            v[k] = out;
+        }
+        if (threadIdx.x == 0 && head == n - 1 && n - 1 < target) { // the list grows: its last element is kept too
+            const int u = lower_bound((unsigned)n << 10) - 1;
+            if (u >= 0 && (key[u] >> 10) == (unsigned)(n - 1)) v[n - 1] = a_of((int)(key[u] & 1023u));
         }
     }
     __syncthreads();

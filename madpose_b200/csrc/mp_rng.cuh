@@ -62,19 +62,48 @@ MP_HD uint32_t mt_next(MtStream *s) {
     s->pos++;
     return mt_temper(y);
 }
+// Word sources: anything with `uint32_t next()` returning the next TEMPERED output word.
+struct MtDirect { // the stream itself (ring in global memory)
+    MtStream *s;
+    MP_HD uint32_t next() { return mt_next(s); }
+    MP_HD unsigned long long position() const { return s->pos; }
+};
+// A window of raw words [pos0, pos0 + cnt) copied out of the ring (shared memory on the device):
+// consumed sequentially by one thread; falls back to the stream when the window is used up.
+struct MtWindow {
+    MtStream *s;
+    const uint32_t *w;
+    unsigned long long pos0;
+    int cnt, used;
+    bool spilled;
+    MP_HD uint32_t next() {
+        if (!spilled) {
+            if (used < cnt) return mt_temper(w[used++]);
+            spilled = true;
+            s->pos = pos0 + (unsigned long long)used;
+        }
+        return mt_next(s);
+    }
+    MP_HD unsigned long long position() const { return spilled ? s->pos : pos0 + (unsigned long long)used; }
+};
+
 // std::uniform_int_distribution<int>(a, b) on a 32-bit engine (libstdc++ 13: Lemire's method)
-MP_HD int mt_uniform_int(MtStream *s, int a, int b) {
+template <class Src> MP_HD int mt_uniform_int_t(Src &s, int a, int b) {
     const uint32_t range = (uint32_t)(b - a) + 1u; // never 0 here (b - a < 2^32 - 1)
-    unsigned long long prod = (unsigned long long)mt_next(s) * range;
+    unsigned long long prod = (unsigned long long)s.next() * range;
     uint32_t low = (uint32_t)prod;
     if (low < range) {
         const uint32_t thr = (0u - range) % range;
         while (low < thr) {
-            prod = (unsigned long long)mt_next(s) * range;
+            prod = (unsigned long long)s.next() * range;
             low = (uint32_t)prod;
         }
     }
     return a + (int)(prod >> 32);
+}
+MP_HD int mt_uniform_int(MtStream *s, int a, int b) {
+    MtDirect d{s};
+    return mt_uniform_int_t(d, a, b);
 }
 // would the word `w` be rejected by uniform_int with this range?
 MP_HD bool mt_lemire_rejects(uint32_t w, uint32_t range) {
@@ -82,16 +111,20 @@ MP_HD bool mt_lemire_rejects(uint32_t w, uint32_t range) {
     return low < range && low < (0u - range) % range;
 }
 // std::uniform_real_distribution<double>(0, hi): generate_canonical<double, 53> = two words
-MP_HD double mt_uniform_real(MtStream *s, double hi) {
-    const double lo32 = (double)mt_next(s), hi32 = (double)mt_next(s);
+template <class Src> MP_HD double mt_uniform_real_t(Src &s, double hi) {
+    const double lo32 = (double)s.next(), hi32 = (double)s.next();
     double c = (lo32 + hi32 * 4294967296.0) / 18446744073709551616.0;
     if (c >= 1.0) c = 1.0 - 1.1102230246251565e-16; // nextafter(1, 0)
     return c * hi; // (b - a) * c + a with a = 0
 }
+MP_HD double mt_uniform_real(MtStream *s, double hi) {
+    MtDirect d{s};
+    return mt_uniform_real_t(d, hi);
+}
 
 // HybridUniformSampling::DrawSample / ShuffleSample for one data type (hybrid_sampling.h:84-131):
 // k distinct indices of [0, n).  scratch: n ints, only touched on the Fisher-Yates branch.
-MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
+template <class Src> MP_HD void mt_draw_sample_t(Src &s, int n, int k, int *out, int *scratch) {
     if (k <= 0) return;
     const double coeff = (double)n / (double)(n - k);
     if (coeff < 2.718281828459045235360287471352662498) {
@@ -99,7 +132,7 @@ MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
             bool dup = true;
             while (dup) {
                 dup = false;
-                out[i] = mt_uniform_int(s, 0, n - 1);
+                out[i] = mt_uniform_int_t(s, 0, n - 1);
                 for (int j = 0; j < i; j++)
                     if (out[j] == out[i]) { dup = true; break; }
             }
@@ -108,11 +141,15 @@ MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
         for (int i = 0; i < n; i++) scratch[i] = i;
         if (k != n)
             for (int i = 0; i < n - 1; i++) {
-                const int j = mt_uniform_int(s, i, n - 1);
+                const int j = mt_uniform_int_t(s, i, n - 1);
                 const int t = scratch[i]; scratch[i] = scratch[j]; scratch[j] = t;
             }
         for (int i = 0; i < k; i++) out[i] = scratch[i];
     }
+}
+MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
+    MtDirect d{s};
+    mt_draw_sample_t(d, n, k, out, scratch);
 }
 
 } // namespace mp
