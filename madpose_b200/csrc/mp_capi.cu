@@ -100,7 +100,9 @@ void mp_destroy(mp_ctx *c) {
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     for (auto &e : c->tick_ev) cudaEventDestroy(e);
     for (auto &e : c->gev) cudaEventDestroy(e);
+    for (auto &e : c->sev) cudaEventDestroy(e);
     for (auto &g : c->gstream) cudaStreamDestroy(g);
+    for (auto &g : c->sstream) cudaStreamDestroy(g);
     if (c->ev_init) cudaEventDestroy(c->ev_init);
     if (c->loop_alloc) delete static_cast<mp::LoopAlloc *>(c->loop_alloc);
     if (c->stream) cudaStreamDestroy(c->stream);

@@ -6,6 +6,8 @@
 
 namespace mp {
 
+constexpr int MP_MAX_GROUPS = 1024;
+
 // PairState -> mp_model / mp_stats; undoes the focal normalisation
 // (...shared_focal_estimator.cpp:49, ...two_focal_estimator.cpp:72-73)
 __global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp_stats *stats) {
@@ -69,29 +71,46 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.inl_cur.reserve((3 * (size_t)N + 4) * sizeof(int)));
     MP_CUDA(A.flat.reserve(2 * (size_t)CAP * sizeof(int)));
     MP_CUDA(A.sample.reserve(3 * (size_t)CAP * sizeof(int)));
-    MP_CUDA(A.misc.reserve(1024));
+    MP_CUDA(A.misc.reserve(128 + 4 * MP_MAX_GROUPS));
     MP_CUDA(A.off3.reserve((n_pairs + 1) * sizeof(long long)));
     MP_CUDA(A.caps.reserve(n_pairs * sizeof(int)));
     MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.out_models.reserve(n_pairs * sizeof(mp_model)));
     MP_CUDA(A.out_stats.reserve(n_pairs * sizeof(mp_stats)));
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
-    MP_CUDA(A.h_active.reserve(1024));
+    MP_CUDA(A.h_active.reserve(4 * MP_MAX_GROUPS));
     LoopParams *prm = A.h_prm.as<LoopParams>();
     prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = LP_BMAX; prm->guard = 1e-3;
-    // groups of consecutive pairs, each driven on its own stream: a group's round waits only for
-    // its own slowest pair, and kernels of different groups overlap on the GPU
-    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 95) / 96;
-    G = std::max(1, std::min(G, c->groups_override > 0 ? 32 : 16));
+    // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
+    // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
+    // waits for them: a pair inside a local optimisation sits the rounds out until its lo_kernel publishes it again.
+    const bool serial = c->groups_override == 1; // one stream, scan and lo back to back (per-class timing pass)
+    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 374) / 375;
+    G = std::max(1, std::min(G, c->groups_override > 0 ? MP_MAX_GROUPS : 8));
     const int gsz = (n_pairs + G - 1) / G;
     G = (n_pairs + gsz - 1) / gsz;
-    int *h_active = A.h_active.as<int>();
-    for (int g = 0; g < G; g++) h_active[g] = std::min(gsz, n_pairs - g * gsz);
+    constexpr int SLOTS = 4, NSIDE = 12;
+    MP_CUDA(A.misc.reserve(128 + 16 * MP_MAX_GROUPS));
+    MP_CUDA(A.items.reserve(2 * (size_t)n_pairs * LP_BMAX * sizeof(int)));
+    MP_CUDA(A.h_active.reserve(4 * (2 + SLOTS) * MP_MAX_GROUPS));
+    MP_CUDA(A.lo_req.reserve(n_pairs * sizeof(int)));
+    int *h_active = A.h_active.as<int>(), *h_iter = h_active + G, *h_side = h_active + 2 * G; // h_side[g * SLOTS + k]
+    for (int g = 0; g < G; g++) { h_active[g] = std::min(gsz, n_pairs - g * gsz); h_iter[g] = 0; }
     while ((int)c->gstream.size() < G) {
         cudaStream_t gs; cudaEvent_t ge;
         MP_CUDA(cudaStreamCreateWithFlags(&gs, cudaStreamNonBlocking));
         MP_CUDA(cudaEventCreateWithFlags(&ge, cudaEventDisableTiming));
         c->gstream.push_back(gs); c->gev.push_back(ge);
+    }
+    while ((int)c->sstream.size() < NSIDE) {
+        cudaStream_t gs;
+        MP_CUDA(cudaStreamCreateWithFlags(&gs, cudaStreamNonBlocking));
+        c->sstream.push_back(gs);
+    }
+    while ((int)c->sev.size() < G * SLOTS) {
+        cudaEvent_t ge;
+        MP_CUDA(cudaEventCreateWithFlags(&ge, cudaEventDisableTiming));
+        c->sev.push_back(ge);
     }
     if (!c->ev_init) MP_CUDA(cudaEventCreateWithFlags(&c->ev_init, cudaEventDisableTiming));
     MP_CUDA(cudaMemcpyAsync(A.prm.p, prm, sizeof(LoopParams), cudaMemcpyHostToDevice, s));
@@ -104,6 +123,10 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.models = A.models.as<Model>(); L.hyps = A.hyps.as<HypF>();
     L.inl_best = A.inl_best.as<int>(); L.inl_cur = A.inl_cur.as<int>(); L.flat = A.flat.as<int>(); L.sample = A.sample.as<int>();
     L.n_active = reinterpret_cast<int *>(A.misc.as<char>() + 128);
+    L.n_iter = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 4 * MP_MAX_GROUPS);
+    L.n_items = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 8 * MP_MAX_GROUPS);
+    L.items = A.items.as<int>(); L.n_pairs = n_pairs;
+    L.lo_req = A.lo_req.as<int>();
     L.gsz = gsz;
     L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>());
     MP_CUDA(cudaMemsetAsync(L.clk, 0, 64, s));
@@ -117,7 +140,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     tile_cap = tile_cap / 32 * 32;
     const size_t smem = (size_t)tile_cap * 32;
     const unsigned max_it = std::max(opt->max_num_iterations, opt->min_num_iterations);
-    const long long max_rounds = 2ll * max_it + 64;
+    const long long max_rounds = 64ll * max_it + 4096;
     long long rounds = 0;
     c->n_tick = 0;
     auto tick = [&](int cls) -> cudaError_t { // event before each kernel class; cls = -1 closes the last interval
@@ -131,60 +154,102 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         return cudaEventRecord(c->tick_ev[c->n_tick++], s);
     };
     MP_CUDA(cudaEventRecord(c->ev_init, s));
-    std::vector<int> act(G), pending(G, 0);
-    std::vector<long long> grounds(G, 0);
+    struct GroupRt {
+        int act = 0, iter = 1;        // latest known: pairs not done; pairs left iterating by the last scan
+        bool main_pending = false, lo_returned = true;
+        bool slot_busy[SLOTS] = {false, false, false, false};
+        long long round = 0;
+    };
+    std::vector<GroupRt> gr(G);
     for (int g = 0; g < G; g++) {
-        act[g] = h_active[g];
-        if (G > 1) MP_CUDA(cudaStreamWaitEvent(c->gstream[g], c->ev_init, 0));
+        gr[g].act = h_active[g];
+        if (!serial) MP_CUDA(cudaStreamWaitEvent(c->gstream[g], c->ev_init, 0));
     }
-    auto enqueue_round = [&](int g) -> int {
-        cudaStream_t gs = G > 1 ? c->gstream[g] : s;
+    if (!serial)
+        for (int k = 0; k < NSIDE; k++) MP_CUDA(cudaStreamWaitEvent(c->sstream[k], c->ev_init, 0));
+    int side_rr = 0;
+    const long long *d_off3 = A.off3.as<long long>();
+    const int *d_caps = A.caps.as<int>();
+    auto enqueue_round = [&](int g, int slot) -> int {
+        cudaStream_t gs = serial ? s : c->gstream[g];
         const int first = g * gsz, count = std::min(gsz, n_pairs - first);
-        const bool timed = G == 1;
-        if (timed) MP_CUDA(tick(0));
+        const int round = (int)(++gr[g].round);
+        MP_CUDA(cudaMemsetAsync(L.n_iter + g, 0, sizeof(int), gs));
+        MP_CUDA(cudaMemsetAsync(L.n_items + 2 * g, 0, 2 * sizeof(int), gs));
+        if (serial) MP_CUDA(tick(0));
         sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
-        if (timed) MP_CUDA(tick(1));
+        if (serial) MP_CUDA(tick(1));
         MP_CUDA(launch_minimal_batch(L, dprm, first, count, gs));
-        if (timed) MP_CUDA(tick(2));
+        if (serial) MP_CUDA(tick(2));
         if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, first, count, tile_cap, smem, gs));
         else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, first, count, tile_cap, smem, gs));
         else MP_CUDA(launch_score_kind<TWO>(L, dprm, first, count, tile_cap, smem, gs));
-        if (timed) MP_CUDA(tick(3));
-        if (kind == CALIB) MP_CUDA(launch_decide_kind<CALIB>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
-        else if (kind == SHARED) MP_CUDA(launch_decide_kind<SHARED>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
-        else MP_CUDA(launch_decide_kind<TWO>(L, dprm, first, count, A.off3.as<long long>(), A.caps.as<int>(), gs));
-        if (timed) MP_CUDA(tick(-1));
-        MP_CUDA(cudaMemcpyAsync(h_active + g, L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, gs));
+        if (serial) MP_CUDA(tick(3));
+        if (kind == CALIB) MP_CUDA(launch_scan_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, gs));
+        else if (kind == SHARED) MP_CUDA(launch_scan_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, gs));
+        else MP_CUDA(launch_scan_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, gs));
+        MP_CUDA(cudaMemcpyAsync(h_iter + g, L.n_iter + g, sizeof(int), cudaMemcpyDeviceToHost, gs));
         MP_CUDA(cudaEventRecord(c->gev[g], gs));
-        launches += 4;
+        cudaStream_t ss = gs;
+        if (!serial) {
+            ss = c->sstream[side_rr++ % NSIDE];
+            MP_CUDA(cudaStreamWaitEvent(ss, c->gev[g], 0));
+        }
+        if (kind == CALIB) MP_CUDA(launch_lo_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, ss));
+        else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, ss));
+        else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, ss));
+        if (serial) MP_CUDA(tick(-1));
+        MP_CUDA(cudaMemcpyAsync(h_side + g * SLOTS + slot, L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
+        MP_CUDA(cudaEventRecord(c->sev[g * SLOTS + slot], ss));
+        launches += 5;
         return MP_OK;
     };
     while (true) {
         bool any = false, progress = false;
         for (int g = 0; g < G; g++) {
-            if (act[g] <= 0 && !pending[g]) continue;
-            any = true;
-            if (pending[g]) {
-                cudaError_t q = cudaEventQuery(c->gev[g]);
-                if (q == cudaErrorNotReady) continue;
+            GroupRt &R = gr[g];
+            bool side_busy = false;
+            for (int k = 0; k < SLOTS; k++) {
+                if (!R.slot_busy[k]) continue;
+                cudaError_t q = cudaEventQuery(c->sev[g * SLOTS + k]);
+                if (q == cudaErrorNotReady) { side_busy = true; continue; }
                 MP_CUDA(q);
-                pending[g] = 0;
-                act[g] = h_active[g];
+                R.slot_busy[k] = false;
+                R.act = std::min(R.act, h_side[g * SLOTS + k]);
+                R.lo_returned = true;
                 progress = true;
-                if (act[g] <= 0) continue;
             }
-            if (++grounds[g] > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
-            int rc2 = enqueue_round(g);
+            if (R.main_pending) {
+                cudaError_t q = cudaEventQuery(c->gev[g]);
+                if (q != cudaErrorNotReady) {
+                    MP_CUDA(q);
+                    R.main_pending = false;
+                    R.iter = h_iter[g];
+                    progress = true;
+                }
+            }
+            if (R.act <= 0 && !R.main_pending && !side_busy) continue; // group finished
+            any = true;
+            if (R.main_pending || R.act <= 0) continue;
+            if (R.iter <= 0 && !R.lo_returned) continue; // nobody iterates; wait for a local optimisation to hand pairs back
+            int slot = -1;
+            for (int k = 0; k < SLOTS; k++)
+                if (!R.slot_busy[k]) { slot = k; break; }
+            if (slot < 0) continue;
+            if (R.round > max_rounds) return fail(MP_ERR_CUDA, "device loop did not terminate");
+            R.lo_returned = false;
+            int rc2 = enqueue_round(g, slot);
             if (rc2) return rc2;
-            pending[g] = 1;
+            R.main_pending = true; R.slot_busy[slot] = true;
             progress = true;
         }
         if (!any) break;
         if (!progress) std::this_thread::yield();
     }
+    std::vector<long long> grounds(G);
+    for (int g = 0; g < G; g++) grounds[g] = gr[g].round;
     for (int g = 0; g < G; g++) rounds = std::max(rounds, grounds[g]);
-    if (G > 1)
-        for (int g = 0; g < G; g++) MP_CUDA(cudaStreamWaitEvent(s, c->gev[g], 0));
+    // every group event has been observed complete by the host: the streams are drained
     finalize_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, n_pairs, A.out_models.as<mp_model>(), A.out_stats.as<mp_stats>());
     MP_CUDA(cudaGetLastError());
     launches += 1;
@@ -295,7 +360,7 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
 }
 int mp_set_groups(mp_ctx *c, int groups) {
     using namespace mp;
-    if (!c || groups < 0 || groups > 32) return fail(MP_ERR_ARG, "mp_set_groups: 0 (automatic) .. 32");
+    if (!c || groups < 0 || groups > MP_MAX_GROUPS) return fail(MP_ERR_ARG, "mp_set_groups: 0 (automatic) .. 1024");
     c->groups_override = groups;
     return MP_OK;
 }

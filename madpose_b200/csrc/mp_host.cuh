@@ -76,8 +76,8 @@ struct mp_ctx {
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     int groups_override = 0, last_groups = 1; // 0 = automatic
-    std::vector<cudaStream_t> gstream;
-    std::vector<cudaEvent_t> gev;
+    std::vector<cudaStream_t> gstream, sstream; // per-group round pipelines; side streams of the lo_kernel launches
+    std::vector<cudaEvent_t> gev, sev;
     cudaEvent_t ev_init = nullptr;
     void *loop_alloc = nullptr; // mp::LoopAlloc, created on first mp_estimate_batch
     uint32_t tape_seed = 0;

@@ -15,13 +15,13 @@ __global__ void __launch_bounds__(MP_CTA, 1) score_batch_kernel(LoopBuffers L, c
     __shared__ int nlist;
     const LoopParams &prm = *prmp;
     const int p = first + blockIdx.x;
-    const PairState &S = L.st[p];
-    if (S.phase != PH_ITER || S.batch_len == 0) return;
-    const PairConst &pc = L.pc[p];
     PairWork &W = L.wk[p];
+    const int blen = W.blen;
+    if (blen == 0) return;
+    const PairConst &pc = L.pc[p];
     if (threadIdx.x == 0) {
         int c = 0;
-        for (int b = 0; b < S.batch_len; b++)
+        for (int b = 0; b < blen; b++)
             for (int j = 0; j < W.count[b]; j++) list[c++] = (unsigned short)(b * LP_MM + j);
         nlist = c;
         mbar_init(&bar, 1);
@@ -69,14 +69,16 @@ template <int KIND> __device__ void block_update_termination(const BlockCtx &C, 
     __syncthreads();
 }
 
-template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) decide_kernel(LoopBuffers L, const LoopParams *prmp,
-                                                                                  const long long *off3, const int *caps, int first) {
+// scan_kernel: the iterations of this round, replayed in order (the PH_ITER part of the loop).  A pair that
+// needs a local optimisation / the final stage leaves with its phase set and a ticket in lo_req; lo_kernel
+// (usually on another stream, so that the other pairs keep iterating meanwhile) picks the ticket up.
+template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) scan_kernel(LoopBuffers L, const LoopParams *prmp,
+                                                                                const long long *off3, const int *caps, int first, int round) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
-    __shared__ double lo_score;
     const LoopParams &prm = *prmp;
     const int p = first + blockIdx.x;
-    if (L.st[p].phase == PH_DONE) return;
+    if (L.wk[p].blen == 0) return; // not iterating this round
     {
         const int *src = reinterpret_cast<const int *>(&L.st[p]);
         int *dst = reinterpret_cast<int *>(&S);
@@ -171,6 +173,58 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
         __syncthreads();
     }
 
+
+    {
+        int *dst = reinterpret_cast<int *>(&L.st[p]);
+        const int *src = reinterpret_cast<const int *>(&S);
+        for (int i = threadIdx.x; i < (int)(sizeof(PairState) / 4); i += blockDim.x) dst[i] = src[i];
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (S.phase == PH_ITER) atomicAdd(L.n_iter + p / L.gsz, 1);
+        else *reinterpret_cast<volatile int *>(L.lo_req + p) = round; // PH_LO_PRE / PH_LO_MAIN / PH_FINISH
+    }
+}
+
+// lo_kernel: local optimisations and the final stage of the pairs holding a ticket of a round <= `round`.
+template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lo_kernel(LoopBuffers L, const LoopParams *prmp,
+                                                                              const long long *off3, const int *caps, int first, int round) {
+    __shared__ PairState S;
+    __shared__ BlockScratch sh;
+    __shared__ double lo_score;
+    __shared__ int claimed;
+    const LoopParams &prm = *prmp;
+    const int p = first + blockIdx.x;
+    if (threadIdx.x == 0) {
+        const int t = *reinterpret_cast<volatile int *>(L.lo_req + p);
+        claimed = (t > 0 && t <= round && atomicCAS(L.lo_req + p, t, -t) == t) ? 1 : 0;
+        __threadfence();
+    }
+    __syncthreads();
+    if (!claimed) return;
+    {
+        const int *src = reinterpret_cast<const int *>(&L.st[p]);
+        int *dst = reinterpret_cast<int *>(&S);
+        for (int i = threadIdx.x; i < (int)(sizeof(PairState) / 4); i += blockDim.x) dst[i] = __ldcg(src + i);
+    }
+    __syncthreads();
+    const PairConst &pc = L.pc[p];
+    PairWork &W = L.wk[p];
+    const Model *models = L.models + (size_t)p * LP_BMAX * LP_MM;
+    MtStream *rA = &L.rngA[p], *rB = &L.rngB[p];
+    const long long o3 = off3[p];
+    int *inl_best = L.inl_best + 3 * pc.off;
+    BlockCtx C;
+    C.pc = &pc; C.M = L.M + pc.off; C.prm = &prm; C.S = &S; C.rngB = rB; C.sh = &sh;
+    C.cap = caps[p];
+    C.inl_cur = L.inl_cur + 3 * pc.off;
+    C.flat = L.flat + 2 * o3; C.base = C.flat + C.cap; C.sample = L.sample + 3 * o3; // o3 = sum of caps of earlier pairs
+    const unsigned lo_start = prm.opt.lo_starting_iterations;
+    const unsigned max_it = prm.opt.max_num_iterations > prm.opt.min_num_iterations ? prm.opt.max_num_iterations
+                                                                                   : prm.opt.min_num_iterations;
+    const int n = pc.n;
+
     while (S.phase == PH_LO_PRE || S.phase == PH_LO_MAIN || S.phase == PH_FINISH) {
         if (S.phase == PH_LO_PRE) {
             if (threadIdx.x == 0) S.number_lo += 1;
@@ -219,14 +273,26 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
         __syncthreads();
     }
 
+
+    // publish: everything but the phase first (the copy carries PH_BUSY), then the ticket, then the phase
+    __shared__ int final_phase;
+    if (threadIdx.x == 0) { final_phase = S.phase; S.phase = PH_BUSY; }
+    __syncthreads();
     {
         int *dst = reinterpret_cast<int *>(&L.st[p]);
         const int *src = reinterpret_cast<const int *>(&S);
         for (int i = threadIdx.x; i < (int)(sizeof(PairState) / 4); i += blockDim.x) dst[i] = src[i];
     }
-    if (threadIdx.x == 0 && S.phase == PH_DONE) {
-        atomicSub(L.n_active + p / L.gsz, 1);
-        for (int q = 0; q < 8; q++) atomicAdd(L.clk + q, S.clk[q]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *reinterpret_cast<volatile int *>(L.lo_req + p) = 0;
+        __threadfence();
+        atomicExch(&L.st[p].phase, final_phase);
+        if (final_phase == PH_DONE) {
+            atomicSub(L.n_active + p / L.gsz, 1);
+            for (int q = 0; q < 8; q++) atomicAdd(L.clk + q, S.clk[q]);
+        }
     }
 }
 
@@ -239,9 +305,15 @@ cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int first, 
     return cudaGetLastError();
 }
 template <int KIND>
-cudaError_t launch_decide_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
-                               const int *caps, cudaStream_t s) {
-    decide_kernel<KIND><<<count, LP_THREADS, 0, s>>>(L, dprm, off3, caps, first);
+cudaError_t launch_scan_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
+                             const int *caps, int round, cudaStream_t s) {
+    scan_kernel<KIND><<<count, LP_THREADS, 0, s>>>(L, dprm, off3, caps, first, round);
+    return cudaGetLastError();
+}
+template <int KIND>
+cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
+                           const int *caps, int round, cudaStream_t s) {
+    lo_kernel<KIND><<<count, LP_THREADS, 0, s>>>(L, dprm, off3, caps, first, round);
     return cudaGetLastError();
 }
 

@@ -2,6 +2,7 @@
 #include "mp_kind.cuh"
 namespace mp {
 template cudaError_t launch_score_kind<2>(LoopBuffers, const LoopParams *, int, int, int, size_t, cudaStream_t);
-template cudaError_t launch_decide_kind<2>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, cudaStream_t);
+template cudaError_t launch_scan_kind<2>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, int, cudaStream_t);
+template cudaError_t launch_lo_kind<2>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, int, cudaStream_t);
 template cudaError_t launch_lm_kind<2>(const PairConst *, const Match64 *, const LoopParams *, int, const Model *, const int *, const int *, Model *, double *, cudaStream_t);
 }

@@ -54,10 +54,12 @@ __device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     return go != 0;
 }
 
-// LmDriver::propose
-__device__ inline bool warp_lm_propose(LmDriver &d, int lane) {
+// LmDriver::propose.  NT > 0: the number of active tangent slots is known at compile time (every slot of the
+// kind is active -- the normal case), the elimination is straight-line code; NT == 0: run-time nt.
+template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane) {
     const LmSetup &L = *d.L;
-    const int nt = L.nt;
+    const int nt = NT > 0 ? NT : L.nt;
+#define LMW_IN(k_) (NT > 0 ? (k_) < NT : (k_) < nt)
     while (true) {
         int stop = 0;
         if (lane == 0) {
@@ -72,81 +74,84 @@ __device__ inline bool warp_lm_propose(LmDriver &d, int lane) {
         __syncwarp();
         const double radius = d.radius;
         const bool rowl = lane < nt;
+        const int rl = rowl ? lane : 0; // idle lanes shadow row 0 (their results are never read)
         // my row of the scaled system; the damped copy stays in registers
         double row[LM_NT];
-        const double sa = rowl ? d.scale[lane] : 0.0;
+        const double sa = d.scale[rl];
 #pragma unroll
         for (int b = 0; b < LM_NT; b++) {
             double v = 0.0;
-            if (rowl && b < nt) {
-                v = d.A[lane * nt + b] * sa * d.scale[b];
-                d.As[lane * nt + b] = v;
+            if (LMW_IN(b)) {
+                v = d.A[rl * nt + b] * sa * d.scale[b];
+                if (rowl) d.As[rl * nt + b] = v;
             }
             row[b] = v;
         }
-        if (rowl) d.gs[lane] = d.g[lane] * sa;
+        const double gsl = d.g[rl] * sa;
+        if (rowl) d.gs[rl] = gsl;
         {
             double diag = 0.0;
 #pragma unroll
             for (int b = 0; b < LM_NT; b++)
-                if (b == lane) diag = row[b];
+                if (b == rl) diag = row[b];
             const double add = fmin(fmax(diag, 1e-6), 1e32) / radius;
 #pragma unroll
             for (int b = 0; b < LM_NT; b++)
-                if (b == lane) row[b] += add;
+                if (b == rl) row[b] += add;
         }
         __syncwarp();
-        // right-looking Cholesky: after step k, row[k] = L[lane][k]
-        bool ok = true;
+        // right-looking Cholesky, no early exit: after step k, row[k] = L[lane][k]; a bad pivot is remembered
+        bool bad = false;
 #pragma unroll
         for (int k = 0; k < LM_NT; k++) {
-            if (k < nt && ok) {
+            if (LMW_IN(k)) {
                 const double dk = __shfl_sync(LMW_FULL, row[k], k);
-                if (!(dk > 0.0) || !finite_d(dk)) ok = false;
-                else {
-                    const double lkk = sqrt(dk);
-                    const double lik = lane == k ? lkk : row[k] / lkk;
-                    row[k] = lik;
+                bad = bad || !(dk > 0.0) || !finite_d(dk);
+                const double lkk = sqrt(dk);
+                const double lik = lane == k ? lkk : row[k] / lkk;
+                row[k] = lik;
 #pragma unroll
-                    for (int j = k + 1; j < LM_NT; j++) {
+                for (int j = k + 1; j < LM_NT; j++) {
+                    if (LMW_IN(j)) {
                         const double ljk = __shfl_sync(LMW_FULL, lik, j);
-                        if (j < nt && j <= lane) row[j] -= lik * ljk;
+                        if (j <= lane) row[j] -= lik * ljk;
                     }
                 }
             }
         }
-        double xs[LM_NT];
-        if (ok) {
-            if (rowl) {
+        if (rowl) {
 #pragma unroll
-                for (int j = 0; j < LM_NT; j++)
-                    if (j <= lane) d.Lc[lane * nt + j] = row[j];
-            }
-            // forward substitution, column-oriented: y_k known -> every later row subtracts L[i][k] y_k
-            double s = rowl ? d.gs[lane] : 0.0;
+            for (int j = 0; j < LM_NT; j++)
+                if (j <= lane) d.Lc[lane * nt + j] = row[j];
+        }
+        // forward substitution, column-oriented: y_k known -> every later row subtracts L[i][k] y_k
+        {
+            double s = gsl;
 #pragma unroll
             for (int k = 0; k < LM_NT; k++) {
-                if (k < nt) {
+                if (LMW_IN(k)) {
                     const double yk = __shfl_sync(LMW_FULL, s / row[k], k);
                     if (lane == k) d.yw[k] = yk;
                     if (lane > k) s -= row[k] * yk;
                 }
             }
-            __syncwarp();
-            // back substitution (every lane, redundantly; sums in the scalar order k = i+1 .. nt-1)
+        }
+        __syncwarp();
+        // back substitution (every lane, redundantly; sums in the scalar order k = i+1 .. nt-1)
+        double xs[LM_NT];
+        bool ok = !bad;
 #pragma unroll
-            for (int i = LM_NT - 1; i >= 0; i--) {
-                double v = 0.0;
-                if (i < nt) {
-                    double t = d.yw[i];
+        for (int i = LM_NT - 1; i >= 0; i--) {
+            double v = 0.0;
+            if (LMW_IN(i)) {
+                double t = d.yw[i];
 #pragma unroll
-                    for (int k = i + 1; k < LM_NT; k++)
-                        if (k < nt) t -= d.Lc[k * nt + i] * xs[k];
-                    v = t / d.Lc[i * nt + i];
-                    if (!finite_d(v)) ok = false;
-                }
-                xs[i] = v;
+                for (int k = i + 1; k < LM_NT; k++)
+                    if (LMW_IN(k)) t -= d.Lc[k * nt + i] * xs[k];
+                v = t / d.Lc[i * nt + i];
+                ok = ok && finite_d(v);
             }
+            xs[i] = v;
         }
         double mcc = 0;
         if (ok) {
@@ -155,11 +160,11 @@ __device__ inline bool warp_lm_propose(LmDriver &d, int lane) {
             for (int a = 0; a < LM_NT; a++) xs[a] = -xs[a];
 #pragma unroll
             for (int a = 0; a < LM_NT; a++) {
-                if (a < nt) {
+                if (LMW_IN(a)) {
                     dg += xs[a] * d.gs[a];
 #pragma unroll
                     for (int b = 0; b < LM_NT; b++)
-                        if (b < nt) dAd += xs[a] * d.As[a * nt + b] * xs[b];
+                        if (LMW_IN(b)) dAd += xs[a] * d.As[a * nt + b] * xs[b];
                 }
             }
             mcc = -(dg + 0.5 * dAd);
@@ -181,14 +186,20 @@ __device__ inline bool warp_lm_propose(LmDriver &d, int lane) {
             double dd[LM_NT];
 #pragma unroll
             for (int a = 0; a < LM_NT; a++) {
-                dd[a] = a < nt ? xs[a] * d.scale[a] : 0.0;
-                if (a < nt) d.y[a] = xs[a];
+                dd[a] = LMW_IN(a) ? xs[a] * d.scale[a] : 0.0;
+                if (LMW_IN(a)) d.y[a] = xs[a];
             }
             lm_plus(L, d.x, dd, d.xc);
         }
         __syncwarp();
         return true;
     }
+#undef LMW_IN
+}
+// NTK = number of tangent slots of the estimator kind (9 calibrated, 10 shared focal, 11 two focals)
+template <int NTK> __device__ __forceinline__ bool warp_lm_propose(LmDriver &d, int lane) {
+    if (d.L->nt == NTK) return warp_lm_propose_t<NTK>(d, lane);
+    return warp_lm_propose_t<0>(d, lane);
 }
 
 // LmDriver::feed

@@ -25,7 +25,7 @@ constexpr int LP_BMAX = 32;            // iterations per pair per round (upper b
 constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
 constexpr int LP_THREADS = 128;        // decide_kernel CTA
 constexpr int LP_CTAS_PER_SM = 2;
-enum { PH_ITER = 0, PH_LO_PRE = 1, PH_LO_MAIN = 2, PH_FINISH = 3, PH_DONE = 4 };
+enum { PH_ITER = 0, PH_LO_PRE = 1, PH_LO_MAIN = 2, PH_FINISH = 3, PH_DONE = 4, PH_BUSY = 5 };
 
 struct LoopParams {
     mp_options opt;
@@ -34,7 +34,7 @@ struct LoopParams {
     double guard; // relative guard band of the fp32 score filter
 };
 
-struct PairState {
+struct alignas(128) PairState { // 128-byte aligned: no cache line is shared between pairs (see sample_kernel)
     int phase, pre_done, B, batch_len;
     unsigned it;             // iterations completed = index of the next iteration
     unsigned iters[2], cap[2];
@@ -55,6 +55,7 @@ struct PairState {
 
 // per-pair work buffers of one round
 struct PairWork {
+    int blen; // iterations of this round (0: the pair does not take part -- not iterating, or inside a local optimisation)
     int solver[LP_BMAX];
     int idx[LP_BMAX][8];
     unsigned long long posA[LP_BMAX], posB[LP_BMAX]; // stream positions AFTER iteration b
@@ -76,6 +77,13 @@ struct LoopBuffers {
     int *flat;      // [3 * off + pad] scratch: flattened inlier list / shuffled sample
     int *sample;    // [3 * off + pad] scratch: un-flattened sample lists
     int *n_active;  // device counters of pairs not yet PH_DONE, one per group of gsz consecutive pairs
+    int *n_iter;    // per group: pairs left in PH_ITER by the last scan kernel
+    int *n_items;   // per group: [2] number of samples of this round per minimal solver (reset every round)
+    int *items;     // [2][n_pairs * LP_BMAX] samples of this round, (pair - first) * LP_BMAX + b, grouped per solver so that
+                    // the warps of the minimal kernel run ONE solver each (a group uses its own slice [first * LP_BMAX, ...))
+    int n_pairs;
+    int *lo_req;    // per pair: 0, or the round whose scan asked for a local optimisation / the final stage
+                    // (negated while an lo_kernel CTA owns the pair)
     int gsz;
     unsigned long long *clk; // [8] phase cycle totals over all pairs (profiling aid)
 };

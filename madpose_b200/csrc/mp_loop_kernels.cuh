@@ -40,6 +40,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
     for (int q = 0; q < 8; q++) S.clk[q] = 0;
     mt_seed(&L.rngA[p], prm.opt.random_seed);
     mt_seed(&L.rngB[p], prm.opt.random_seed);
+    L.lo_req[p] = 0; L.wk[p].blen = 0;
     if (S.phase == PH_DONE) atomicSub(L.n_active + p / L.gsz, 1);
 }
 
@@ -68,11 +69,16 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
     const int q = blockIdx.x * SMP_WARPS + warp, p = first + q;
     if (q >= count) return;
     PairState &S = L.st[p];
-    if (S.phase != PH_ITER) {
-        if (lane == 0) S.batch_len = 0;
+    PairWork &W = L.wk[p];
+    // the phase is published last by the kernel that owned the pair (lo_kernel: fence, then phase), so a pair seen
+    // in PH_ITER has all its state visible; a pair inside a local optimisation simply sits this round out
+    int ph = 0;
+    if (lane == 0) { ph = *reinterpret_cast<volatile int *>(&S.phase); __threadfence(); }
+    ph = __shfl_sync(0xffffffffu, ph, 0);
+    if (ph != PH_ITER) {
+        if (lane == 0) W.blen = 0;
         return;
     }
-    PairWork &W = L.wk[p];
     MtStream *A = &L.rngA[p], *B = &L.rngB[p];
     const int n = L.pc[p].n;
     const unsigned max_it = prm.opt.max_num_iterations > prm.opt.min_num_iterations ? prm.opt.max_num_iterations
@@ -88,6 +94,7 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
     int sizes[2][3];
     for (int s = 0; s < 2; s++)
         for (int t = 0; t < 3; t++) sizes[s][t] = S.sizes[s][t];
+    unsigned mask1 = 0; // iterations that drew solver 1
     for (unsigned b = 0; b < len; b++) {
         const double u = mt_uniform_real_t(sb, prior0 + prior1);
         int s = -1;
@@ -108,10 +115,21 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
                 for (int i = 0; i < k; i++) W.idx[b][i] = tmp[i];
         }
         W.solver[b] = s;
+        if (s == 1) mask1 |= 1u << b;
         W.posA[b] = sa.position(); W.posB[b] = sb.position();
+    }
+    { // hand the samples to the minimal kernel, one list per solver
+        const int g = p / L.gsz, n1 = __popc(mask1), n0 = (int)len - n1;
+        int o0 = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1 = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
+        int *it0 = L.items + (size_t)first * LP_BMAX, *it1 = L.items + (size_t)(L.n_pairs + first) * LP_BMAX;
+        for (unsigned b = 0; b < len; b++) {
+            if ((mask1 >> b) & 1u) it1[o1++] = q * LP_BMAX + (int)b;
+            else it0[o0++] = q * LP_BMAX + (int)b;
+        }
     }
     A->pos = sa.position(); B->pos = sb.position();
     S.batch_len = (int)len;
+    W.blen = (int)len;
 }
 
 } // namespace mp

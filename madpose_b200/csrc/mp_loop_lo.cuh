@@ -99,9 +99,10 @@ template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L
     __syncthreads();
     if (sh->lm_go) {
         const int lane = threadIdx.x & 31;
+        constexpr int NTK = KIND == CALIB ? 9 : (KIND == SHARED ? 10 : 11);
         ev();
         if (threadIdx.x < 32) { // warp 0 drives (mp_lm_warp.cuh); the other warps wait at the barrier
-            const bool go = warp_lm_first(drv, sh->total, lane) && warp_lm_propose(drv, lane);
+            const bool go = warp_lm_first(drv, sh->total, lane) && warp_lm_propose<NTK>(drv, lane);
             if (lane == 0) sh->lm_go = go ? 1 : 0;
             if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
         }
@@ -109,7 +110,7 @@ template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L
         while (sh->lm_go) {
             ev();
             if (threadIdx.x < 32) {
-                const bool go = warp_lm_feed(drv, sh->total, lane) && warp_lm_propose(drv, lane);
+                const bool go = warp_lm_feed(drv, sh->total, lane) && warp_lm_propose<NTK>(drv, lane);
                 if (lane == 0) sh->lm_go = go ? 1 : 0;
                 if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
             }

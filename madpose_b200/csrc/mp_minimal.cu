@@ -25,16 +25,20 @@ __global__ void __launch_bounds__(64) minimal_kernel(const PairConst *pcp, const
     for (int j = 0; j < c; j++) out[(size_t)s * max_models + j] = tmp[j];
 }
 
-// ---- K1/K2 over all samples of the round: one thread per (pair, iteration)
+// ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
+// sample kernel filled (solver 0 first, solver 1 from the next multiple of 32: a warp runs one solver only)
 __global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    const int p = first + g / LP_BMAX, b = g % LP_BMAX;
-    if (g / LP_BMAX >= count) return;
-    const PairState &S = L.st[p];
-    if (S.phase != PH_ITER || b >= S.batch_len) return;
-    const PairConst &pc = L.pc[p];
+    const int grp = first / L.gsz;
+    const int n0 = L.n_items[2 * grp], n1 = L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
+    int item;
+    if (g < n0) item = L.items[(size_t)first * LP_BMAX + g];
+    else if (g >= n0p && g < n0p + n1) item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + (g - n0p)];
+    else return;
+    const int p = first + item / LP_BMAX, b = item % LP_BMAX;
     PairWork &W = L.wk[p];
+    const PairConst &pc = L.pc[p];
     Model tmp[LP_MM];
     const int c = minimal_solver_ni(pc, L.M + pc.off, W.solver[b], W.idx[b], prm.cfg.min_depth_constraint != 0, tmp);
     W.count[b] = c;
@@ -45,7 +49,7 @@ __global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const 
 
 
 cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, cudaStream_t s) {
-    minimal_batch_kernel<<<(count * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
+    minimal_batch_kernel<<<(count * LP_BMAX + 32 + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
     return cudaGetLastError();
 }
 

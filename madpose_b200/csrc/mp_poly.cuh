@@ -88,38 +88,47 @@ template <int MAXD> MP_HD int real_roots_unscaled(const double *pin, int n, doub
         if (c0 - c1 <= 0) return 0;
         lo_s[0] = -B; hi_s[0] = B; cl_s[0] = c0; ch_s[0] = c1; sp = 1;
     }
-    while (sp > 0 && nroots < MAXD) {
+    // phase 1: isolation only (every lane of a warp is in the same loop: bisect on the sign-change count);
+    // isolated intervals are queued in the order the one-pass version would have refined them
+    double qlo[MAXD + 1], qhi[MAXD + 1];
+    int nq = 0;
+    while (sp > 0 && nq < MAXD) {
         sp--;
         const double ilo = lo_s[sp], ihi = hi_s[sp];
         const int clo = cl_s[sp], chi = ch_s[sp], nr = clo - chi;
         if (nr <= 0) continue;
         if (nr == 1 || (ihi - ilo) < 1e-14 * (1.0 + fabs(ilo))) {
-            double lo = ilo, hi = ihi, flo = poly_val(p, n, lo), fhi = poly_val(p, n, hi);
-            double x = 0.5 * (lo + hi);
-            if (flo * fhi <= 0) {
-                for (int it = 0; it < 200 && hi - lo > 1e-15 * (1.0 + fabs(x)); it++) {
-                    x = 0.5 * (lo + hi);
-                    double fx = poly_val(p, n, x);
-                    if (fx == 0.0) break;
-                    if ((fx < 0) == (flo < 0)) { lo = x; flo = fx; } else hi = x;
-                }
-                x = 0.5 * (lo + hi);
-            }
-            for (int it = 0; it < 8; it++) {
-                double d, f = poly_val_d(p, n, x, &d);
-                if (d == 0.0) break;
-                double xn = x - f / d;
-                if (!(xn >= ilo && xn <= ihi)) break;
-                if (xn == x) break;
-                x = xn;
-            }
-            roots[nroots++] = x;
+            qlo[nq] = ilo; qhi[nq] = ihi; nq++;
             continue;
         }
         const double mid = 0.5 * (ilo + ihi);
         const int cm = sc.changes(mid);
         if (cm - chi > 0 && sp < MAXD + 2) { lo_s[sp] = mid; hi_s[sp] = ihi; cl_s[sp] = cm; ch_s[sp] = chi; sp++; }
         if (clo - cm > 0 && sp < MAXD + 2) { lo_s[sp] = ilo; hi_s[sp] = mid; cl_s[sp] = clo; ch_s[sp] = cm; sp++; }
+    }
+    // phase 2: refinement of every isolated interval (bisection, then Newton)
+    for (int r = 0; r < nq; r++) {
+        const double ilo = qlo[r], ihi = qhi[r];
+        double lo = ilo, hi = ihi, flo = poly_val(p, n, lo), fhi = poly_val(p, n, hi);
+        double x = 0.5 * (lo + hi);
+        if (flo * fhi <= 0) {
+            for (int it = 0; it < 200 && hi - lo > 1e-15 * (1.0 + fabs(x)); it++) {
+                x = 0.5 * (lo + hi);
+                double fx = poly_val(p, n, x);
+                if (fx == 0.0) break;
+                if ((fx < 0) == (flo < 0)) { lo = x; flo = fx; } else hi = x;
+            }
+            x = 0.5 * (lo + hi);
+        }
+        for (int it = 0; it < 8; it++) {
+            double d, f = poly_val_d(p, n, x, &d);
+            if (d == 0.0) break;
+            double xn = x - f / d;
+            if (!(xn >= ilo && xn <= ihi)) break;
+            if (xn == x) break;
+            x = xn;
+        }
+        roots[nroots++] = x;
     }
     for (int i = 1; i < nroots; i++) { // insertion sort (already ascending except for clustered roots)
         double v = roots[i];

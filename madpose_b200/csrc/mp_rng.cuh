@@ -13,7 +13,7 @@ namespace mp {
 
 constexpr int MT_N = 624, MT_M = 397, MT_RING = 4 * MT_N;
 
-struct MtStream {
+struct alignas(128) MtStream { // line-aligned: rings of neighbouring pairs never share a cache line
     uint32_t x[MT_RING];
     unsigned long long gen; // raw words generated so far (multiple of 624, >= 624)
     unsigned long long pos; // raw index of the next output word (>= 624)
