@@ -92,7 +92,7 @@ struct LoopBuffers {
 // (blockDim.x <= 512, all threads participate)
 
 // exact ScoreModel (hybrid_ransac.h:265-282) of one model by the whole CTA
-__device__ __forceinline__ double block_score64(const PairConst &pc, const Match64 *m, const Model &model,
+static __device__ __noinline__ double block_score64(const PairConst &pc, const Match64 *m, const Model &model,
                                                 int score_type, double *red) {
     Eval64 e;
     make_eval64(pc, model, &e);
@@ -108,41 +108,75 @@ __device__ __forceinline__ double block_score64(const PairConst &pc, const Match
 }
 
 // GetInliers (hybrid_ransac.h:289-349): three ascending index lists, out_idx[t * n + k];
-// counts written to cnt_sh[3] (shared).  wcnt: shared int[3][16].
-__device__ __forceinline__ void block_inliers(const PairConst &pc, const Match64 *m, const Model &model,
-                                              const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16]) {
+// counts written to cnt_sh[3] (shared).  wcnt: shared int[3][16] (unused; kept for the callers' layout).
+// Two passes per super-chunk of INL_CH * blockDim matches with no barrier inside the passes:
+//   pass 1  residuals -> 3 flag bits per match kept in registers; per (chunk, warp, type) inlier counts to shared
+//   scan    exclusive prefix of the counts in (chunk, warp) order, one warp per type
+//   pass 2  ranks = prefix + popc(ballot below my lane) -> ordered, conflict-free stores
+constexpr int INL_CH = 16, INL_MAXW = 8;
+struct InlScratch { int cnt[3][INL_CH * INL_MAXW]; int base[3]; };
+static __device__ __noinline__ void block_inliers(const PairConst &pc, const Match64 *m, const Model &model,
+                                           const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16]) {
+    __shared__ InlScratch isc;
     Eval64 e;
     make_eval64(pc, model, &e);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5; // nw <= INL_MAXW
+    const int n = pc.n;
+    const double t0 = thr3[0], t1 = thr3[1], t2 = thr3[2];
     __syncthreads();
-    if (threadIdx.x < 3) cnt_sh[threadIdx.x] = 0;
+    if (threadIdx.x < 3) isc.base[threadIdx.x] = 0;
     __syncthreads();
-    for (int start = 0; start < pc.n; start += blockDim.x) {
-        const int i = start + threadIdx.x;
-        bool in[3] = {false, false, false};
-        if (i < pc.n) {
-            const Match64 mm = m[i];
-            for (int t = 0; t < 3; t++) in[t] = eval64(e, mm, t) < thr3[t];
-        }
-        unsigned bal[3];
-        for (int t = 0; t < 3; t++) {
-            bal[t] = __ballot_sync(0xffffffffu, in[t]);
-            if (lane == 0) wcnt[t][warp] = __popc(bal[t]);
+    for (int sbase = 0; sbase < n; sbase += INL_CH * blockDim.x) {
+        unsigned long long flags = 0;
+#pragma unroll 4
+        for (int c = 0; c < INL_CH; c++) {
+            const int i = sbase + c * blockDim.x + threadIdx.x;
+            unsigned f = 0;
+            if (i < n) {
+                const Match64 mm = m[i];
+                f = (eval64(e, mm, 0) < t0 ? 1u : 0u) | (eval64(e, mm, 1) < t1 ? 2u : 0u) | (eval64(e, mm, 2) < t2 ? 4u : 0u);
+            }
+            flags |= (unsigned long long)f << (3 * c);
+            const unsigned b0 = __ballot_sync(0xffffffffu, f & 1u), b1 = __ballot_sync(0xffffffffu, f & 2u),
+                           b2 = __ballot_sync(0xffffffffu, f & 4u);
+            if (lane == 0) {
+                isc.cnt[0][c * nw + warp] = __popc(b0); isc.cnt[1][c * nw + warp] = __popc(b1); isc.cnt[2][c * nw + warp] = __popc(b2);
+            }
         }
         __syncthreads();
-        for (int t = 0; t < 3; t++) {
-            int off = cnt_sh[t];
-            for (int w = 0; w < warp; w++) off += wcnt[t][w];
-            if (in[t]) out_idx[t * pc.n + off + __popc(bal[t] & ((1u << lane) - 1u))] = i;
+        if (warp < 3) { // exclusive scan of INL_CH * nw counts of type `warp`, starting at the running base
+            int run = isc.base[warp];
+            const int tot = INL_CH * nw;
+            for (int o = 0; o < tot; o += 32) {
+                const int k = o + lane;
+                const int v = k < tot ? isc.cnt[warp][k] : 0;
+                int inc = v;
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int u = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += u;
+                }
+                if (k < tot) isc.cnt[warp][k] = run + inc - v;
+                run += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            __syncwarp();
+            if (lane == 0) isc.base[warp] = run;
         }
         __syncthreads();
-        if (threadIdx.x < 3) {
-            int s = 0;
-            for (int w = 0; w < nw; w++) s += wcnt[threadIdx.x][w];
-            cnt_sh[threadIdx.x] += s;
+#pragma unroll 4
+        for (int c = 0; c < INL_CH; c++) {
+            const int i = sbase + c * blockDim.x + threadIdx.x;
+            const unsigned f = (unsigned)(flags >> (3 * c)) & 7u;
+            const unsigned below = (1u << lane) - 1u;
+            const unsigned b0 = __ballot_sync(0xffffffffu, f & 1u), b1 = __ballot_sync(0xffffffffu, f & 2u),
+                           b2 = __ballot_sync(0xffffffffu, f & 4u);
+            if (f & 1u) out_idx[isc.cnt[0][c * nw + warp] + __popc(b0 & below)] = i;
+            if (f & 2u) out_idx[n + isc.cnt[1][c * nw + warp] + __popc(b1 & below)] = i;
+            if (f & 4u) out_idx[2 * n + isc.cnt[2][c * nw + warp] + __popc(b2 & below)] = i;
         }
         __syncthreads();
     }
+    if (threadIdx.x < 3) cnt_sh[threadIdx.x] = isc.base[threadIdx.x];
+    __syncthreads();
 }
 
 // utils::NumRequiredIterations (ext/RansacLib/RansacLib/utils.h:142-178), vector form

@@ -45,7 +45,7 @@ template <int KIND> struct BlockEval {
     const LmSetup *L;
     const int *lst[3];
     int n[3];
-    __device__ void operator()() const {
+    __device__ __noinline__ void operator()() const {
         MP_CLK_BEGIN();
         BlockScratch *sh = C->sh;
         LmPoint p;
@@ -84,7 +84,7 @@ static_assert(sizeof(LmAcc) == LM_ACC_DOUBLES * sizeof(double), "LmAcc is a flat
 
 // One LM solve by the CTA: warp 0 runs the driver (LmDriver state, mp_lm_warp.cuh), everybody evaluates.
 // x0 -> x (final parameters, valid on thread 0 only); returns info on thread 0.
-template <int KIND> __device__ void block_lm(const BlockCtx &C, const LmSetup &L, const BlockEval<KIND> &ev,
+template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, const LmSetup &L, const BlockEval<KIND> &ev,
                                              const Model &start, Model *out, LmInfo *info_out) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
@@ -151,7 +151,7 @@ template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, 
 //      and resolved sequentially for that one draw);
 //  (2) the first head = min(target, n-1) swaps are replayed in parallel from prefetched
 //      original values (see "Parallel replay" below).
-__device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *v, int *len_sh) {
+static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int target, int *v, int *len_sh) {
     MP_CLK_BEGIN();
     MtStream *g = C.rngB;
     BlockScratch *sh = C.sh;
@@ -269,7 +269,7 @@ __device__ inline void block_shuffle_resize(const BlockCtx &C, int target, int *
 
 // un-flatten (hybrid_ransac.h:443-449, 528-534): entry e -> (type e / n, index e % n), order kept.
 // Stable three-way partition by ballot + prefix counts, one chunk of blockDim entries at a time.
-__device__ inline void block_unflatten(const BlockCtx &C, const int *flat, int len, int *cnt3_sh) {
+static __device__ __noinline__ void block_unflatten(const BlockCtx &C, const int *flat, int len, int *cnt3_sh) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;
@@ -307,7 +307,7 @@ __device__ inline void block_unflatten(const BlockCtx &C, const int *flat, int l
 }
 
 // LeastSquaresFit (hybrid_ransac.h:484-538)
-template <int KIND> __device__ void block_lsq_fit(const BlockCtx &C, const double *thr, int solver, Model *m,
+template <int KIND> __device__ __noinline__ void block_lsq_fit(const BlockCtx &C, const double *thr, int solver, Model *m,
                                                   bool all_inliers) {
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;

@@ -38,12 +38,15 @@ template <int N> MP_HD void jacobi_cols(double *A, double *V) {
                     a = fma(x, x, a); b = fma(y, y, b); c = fma(x, y, c);
                 }
                 double lim = sqrt(a * b);
-                if (!(fabs(c) > 1e-300) || !(fabs(c) > 1e-17 * lim)) continue;
+                // a converged pair is "rotated" by the identity instead of skipped: the lanes of a warp stay
+                // together (1 * x - 0 * y == x exactly, so the result is the one of the skipping form)
+                const bool skip = !(fabs(c) > 1e-300) || !(fabs(c) > 1e-17 * lim);
                 double rel = fabs(c) / lim;
-                off = rel > off ? rel : off;
+                off = (!skip && rel > off) ? rel : off;
                 double zeta = (b - a) / (2.0 * c);
                 double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
                 double cs = 1.0 / sqrt(1.0 + t * t), sn = cs * t;
+                if (skip) { cs = 1.0; sn = 0.0; }
                 for (int k = 0; k < N; k++) {
                     double x = A[k * N + p], y = A[k * N + q];
                     A[k * N + p] = cs * x - sn * y; A[k * N + q] = sn * x + cs * y;
