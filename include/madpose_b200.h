@@ -122,10 +122,13 @@ int mp_estimate_resident(mp_ctx *ctx, const mp_options *opt, const mp_config *cf
 /* per kernel class of the last estimate call: device ms (CUDA events) and launch counts for
  * {sampling, minimal solvers, fp32 scoring, decide (fp64 re-score + inliers + LO/LM)}; rounds */
 int mp_last_breakdown(mp_ctx *ctx, double *class_ms4, int *class_launches4, int *rounds);
-/* The loop runs the batch as `groups` groups of consecutive pairs, each on its own CUDA stream, so that a round
- * of one group waits only for that group's slowest pair.  0 = automatic (about 96 pairs per group, at most 16 groups); 1 = one
- * stream (per-class kernel timings of mp_last_breakdown are exact only then). */
+/* The loop runs the batch as `groups` groups of consecutive pairs, each with its own round pipeline (sampling, minimal
+ * solvers, scoring, scan) on its own CUDA stream; local optimisations run on side streams and never hold a round up.
+ * 0 = automatic (about 750 pairs per group, at most 8 groups); 1 = everything on one stream (the per-class kernel
+ * timings of mp_last_breakdown are exact only then). */
 int mp_set_groups(mp_ctx *ctx, int groups);
+/* RANSAC iterations speculated per pair per round (1..64; 0 = default 64).  Results do not depend on it. */
+int mp_set_batch(mp_ctx *ctx, int iterations);
 /* profiling aid: SM-clock cycles (one thread per pair's CTA, summed over pairs) the decide kernel spent in
  * {sequential scan, GetInliers, fp64 ScoreModel, LM evaluation, LM solves total, shuffles, un-flatten, LO total} */
 int mp_last_phase_cycles(mp_ctx *ctx, unsigned long long *cycles8);

@@ -123,7 +123,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
-    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
+    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
 ]
 
 
@@ -265,6 +265,9 @@ class Context:
         self._check(self.lib.mp_last_phase_cycles(self.ctx, a))
         names = ["scan", "inliers", "score64", "lm_eval", "lm_total", "shuffle", "unflatten", "lo_total"]
         return {k: int(a[i]) for i, k in enumerate(names)}
+
+    def set_batch(self, iterations):
+        self._check(self.lib.mp_set_batch(self.ctx, int(iterations)))
 
     def set_groups(self, groups):
         self._check(self.lib.mp_set_groups(self.ctx, int(groups)))

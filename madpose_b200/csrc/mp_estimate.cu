@@ -3,6 +3,9 @@
 #include "mp_loop_kernels.cuh"
 #include <algorithm>
 #include <thread>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 namespace mp {
 
@@ -80,12 +83,12 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.h_active.reserve(4 * MP_MAX_GROUPS));
     LoopParams *prm = A.h_prm.as<LoopParams>();
-    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = LP_BMAX; prm->guard = 1e-3;
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BMAX; prm->guard = 1e-3;
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
     // waits for them: a pair inside a local optimisation sits the rounds out until its lo_kernel publishes it again.
     const bool serial = c->groups_override == 1; // one stream, scan and lo back to back (per-class timing pass)
-    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 374) / 375;
+    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 749) / 750;
     G = std::max(1, std::min(G, c->groups_override > 0 ? MP_MAX_GROUPS : 8));
     const int gsz = (n_pairs + G - 1) / G;
     G = (n_pairs + gsz - 1) / gsz;
@@ -204,6 +207,9 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         launches += 5;
         return MP_OK;
     };
+    const bool trace = getenv("MP_TRACE") != nullptr; // host-side timeline of the rounds on stderr (debugging aid)
+    const auto t_start = std::chrono::steady_clock::now();
+    auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count(); };
     while (true) {
         bool any = false, progress = false;
         for (int g = 0; g < G; g++) {
@@ -217,6 +223,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
                 R.slot_busy[k] = false;
                 R.act = std::min(R.act, h_side[g * SLOTS + k]);
                 R.lo_returned = true;
+                if (trace) fprintf(stderr, "[mp] %8.2f ms  g%d  lo slot %d done   act %d\n", now_ms(), g, k, R.act);
                 progress = true;
             }
             if (R.main_pending) {
@@ -226,6 +233,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
                     R.main_pending = false;
                     R.iter = h_iter[g];
                     progress = true;
+                    if (trace) fprintf(stderr, "[mp] %8.2f ms  g%d  round %lld done  iterating %d  act %d\n", now_ms(), g, R.round, R.iter, R.act);
                 }
             }
             if (R.act <= 0 && !R.main_pending && !side_busy) continue; // group finished
@@ -357,6 +365,12 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
     if (rc) return rc;
     c->resident_kind = kind; c->resident_pairs = n_pairs;
     return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, false);
+}
+int mp_set_batch(mp_ctx *c, int iterations) {
+    using namespace mp;
+    if (!c || iterations < 0 || iterations > LP_BMAX) return fail(MP_ERR_ARG, "mp_set_batch: 0 (default) .. 64");
+    c->batch_override = iterations;
+    return MP_OK;
 }
 int mp_set_groups(mp_ctx *c, int groups) {
     using namespace mp;

@@ -76,6 +76,7 @@ struct mp_ctx {
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     int groups_override = 0, last_groups = 1; // 0 = automatic
+    int batch_override = 0;                   // speculated iterations per pair per round, 0 = LP_BMAX
     std::vector<cudaStream_t> gstream, sstream; // per-group round pipelines; side streams of the lo_kernel launches
     std::vector<cudaEvent_t> gev, sev;
     cudaEvent_t ev_init = nullptr;

@@ -2,6 +2,7 @@
 // their launchers; instantiated once per kind in mp_kind{0,1,2}.cu so the three variants
 // compile in parallel.
 #pragma once
+#include <cstdlib>
 #include "mp_loop.cuh"
 
 namespace mp {
@@ -313,7 +314,10 @@ cudaError_t launch_scan_kind(LoopBuffers L, const LoopParams *dprm, int first, i
 template <int KIND>
 cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
                            const int *caps, int round, cudaStream_t s) {
-    lo_kernel<KIND><<<count, LP_THREADS, 0, s>>>(L, dprm, off3, caps, first, round);
+    // CTA size of the local optimisation: 128 measured best on configs[1] (64: 4 CTAs per SM but 12 % slower per step,
+    // 32: worse); MP_LO_THREADS overrides it for experiments
+    static const int lo_threads = [] { const char *e = getenv("MP_LO_THREADS"); const int v = e ? atoi(e) : LP_THREADS; return (v == 32 || v == 64 || v == 128) ? v : LP_THREADS; }();
+    lo_kernel<KIND><<<count, lo_threads, 0, s>>>(L, dprm, off3, caps, first, round);
     return cudaGetLastError();
 }
 

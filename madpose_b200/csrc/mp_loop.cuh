@@ -21,7 +21,7 @@
 
 namespace mp {
 
-constexpr int LP_BMAX = 32;            // iterations per pair per round (upper bound)
+constexpr int LP_BMAX = 64;            // iterations per pair per round (upper bound)
 constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
 constexpr int LP_THREADS = 128;        // decide_kernel CTA
 constexpr int LP_CTAS_PER_SM = 2;
@@ -144,22 +144,22 @@ static __device__ __noinline__ void block_inliers(const PairConst &pc, const Mat
             }
         }
         __syncthreads();
-        if (warp < 3) { // exclusive scan of INL_CH * nw counts of type `warp`, starting at the running base
-            int run = isc.base[warp];
+        for (int ty = warp; ty < 3; ty += nw) { // exclusive scan of the INL_CH * nw counts of type ty, from the running base
+            int run = isc.base[ty];
             const int tot = INL_CH * nw;
             for (int o = 0; o < tot; o += 32) {
                 const int k = o + lane;
-                const int v = k < tot ? isc.cnt[warp][k] : 0;
+                const int v = k < tot ? isc.cnt[ty][k] : 0;
                 int inc = v;
                 for (int d = 1; d < 32; d <<= 1) {
                     const int u = __shfl_up_sync(0xffffffffu, inc, d);
                     if (lane >= d) inc += u;
                 }
-                if (k < tot) isc.cnt[warp][k] = run + inc - v;
+                if (k < tot) isc.cnt[ty][k] = run + inc - v;
                 run += __shfl_sync(0xffffffffu, inc, 31);
             }
             __syncwarp();
-            if (lane == 0) isc.base[warp] = run;
+            if (lane == 0) isc.base[ty] = run;
         }
         __syncthreads();
 #pragma unroll 4

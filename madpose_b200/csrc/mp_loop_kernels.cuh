@@ -49,7 +49,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
 // generator rings far enough for the whole batch and copy the raw words the batch can
 // consume into shared-memory windows; lane 0 then draws sequentially from the windows
 // (the draws of one stream are inherently sequential: rejection sampling).
-constexpr int SMP_WARPS = 4, SMP_WIN_A = 640, SMP_WIN_B = 96;
+constexpr int SMP_WARPS = 4, SMP_WIN_A = 20 * LP_BMAX, SMP_WIN_B = 2 * LP_BMAX + 32;
 
 __device__ inline void warp_fill_window(MtStream *g, uint32_t *win, int need, int lane) {
     while (g->gen < g->pos + (unsigned long long)need) mt_refill(g, lane, 32, [] { __syncwarp(); });
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
     int sizes[2][3];
     for (int s = 0; s < 2; s++)
         for (int t = 0; t < 3; t++) sizes[s][t] = S.sizes[s][t];
-    unsigned mask1 = 0; // iterations that drew solver 1
+    unsigned long long mask1 = 0; // iterations that drew solver 1
     for (unsigned b = 0; b < len; b++) {
         const double u = mt_uniform_real_t(sb, prior0 + prior1);
         int s = -1;
@@ -115,15 +115,15 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
                 for (int i = 0; i < k; i++) W.idx[b][i] = tmp[i];
         }
         W.solver[b] = s;
-        if (s == 1) mask1 |= 1u << b;
+        if (s == 1) mask1 |= 1ull << b;
         W.posA[b] = sa.position(); W.posB[b] = sb.position();
     }
     { // hand the samples to the minimal kernel, one list per solver
-        const int g = p / L.gsz, n1 = __popc(mask1), n0 = (int)len - n1;
+        const int g = p / L.gsz, n1 = __popcll(mask1), n0 = (int)len - n1;
         int o0 = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1 = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
         int *it0 = L.items + (size_t)first * LP_BMAX, *it1 = L.items + (size_t)(L.n_pairs + first) * LP_BMAX;
         for (unsigned b = 0; b < len; b++) {
-            if ((mask1 >> b) & 1u) it1[o1++] = q * LP_BMAX + (int)b;
+            if ((mask1 >> b) & 1ull) it1[o1++] = q * LP_BMAX + (int)b;
             else it0[o0++] = q * LP_BMAX + (int)b;
         }
     }

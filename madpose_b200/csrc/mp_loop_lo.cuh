@@ -71,10 +71,10 @@ template <int KIND> struct BlockEval {
             if (lane == 0) sh->part[warp][v] = s;
         }
         __syncthreads();
-        if (threadIdx.x < LM_ACC_DOUBLES) {
+        for (int v = threadIdx.x; v < LM_ACC_DOUBLES; v += blockDim.x) { // any CTA size
             double s = 0;
-            for (int w = 0; w < nw; w++) s += sh->part[w][threadIdx.x];
-            sh->total[threadIdx.x] = s;
+            for (int w = 0; w < nw; w++) s += sh->part[w][v];
+            sh->total[v] = s;
         }
         __syncthreads();
         MP_CLK_END(*C, 3);

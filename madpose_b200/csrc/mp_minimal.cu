@@ -4,6 +4,9 @@
 #include "mp_loop.cuh"
 #include "mp_minimal.cuh"
 
+#ifndef MP_MIN_CTAS
+#define MP_MIN_CTAS 8
+#endif
 namespace mp {
 
 __device__ __noinline__ int minimal_solver_ni(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx,
@@ -27,7 +30,7 @@ __global__ void __launch_bounds__(64) minimal_kernel(const PairConst *pcp, const
 
 // ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
 // sample kernel filled (solver 0 first, solver 1 from the next multiple of 32: a warp runs one solver only)
-__global__ void __launch_bounds__(64) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     const int grp = first / L.gsz;

@@ -114,3 +114,29 @@ def test_rejects_unimplemented_flags(ctx):
     opt.use_ours = 1
     with pytest.raises(RuntimeError, match="not implemented"):
         ctx.estimate_batch(0, [pair], opt, cfg)
+
+
+def test_schedule_invariance(ctx):
+    """The result of a pair must not depend on how the device loop is scheduled: iterations speculated per round
+    (mp_set_batch), number of stream groups (mp_set_groups; 1 = everything on one stream), i.e. on which round a pair
+    sits out while its local optimisation runs on a side stream.  Bit-for-bit."""
+    ps = [problem(1, p=i, n=700) for i in range(24)]
+    kind, opt, cfg = ps[0][0]["kind"], ps[0][2], ps[0][3]
+    pairs = [q[1] for q in ps]
+    ref = None
+    try:
+        for batch, groups in [(0, 0), (8, 1), (64, 5), (17, 24), (32, 2)]:
+            ctx.set_batch(batch); ctx.set_groups(groups)
+            m, s, inl = ctx.estimate_batch(kind, pairs, opt, cfg)
+            sig = [(x.num_iterations_total, tuple(x.num_iterations_per_solver), x.number_lo_iterations, x.best_solver_type,
+                    x.best_model_score, x.best_num_inliers) for x in s]
+            if ref is None:
+                ref = (m.copy(), sig, inl)
+                continue
+            assert sig == ref[1], f"statistics changed with batch={batch} groups={groups}"
+            np.testing.assert_array_equal(m, ref[0])
+            for a, b in zip(inl, ref[2]):
+                for x, y in zip(a, b):
+                    np.testing.assert_array_equal(x, y)
+    finally:
+        ctx.set_batch(0); ctx.set_groups(0)
