@@ -62,13 +62,26 @@ template <int KIND> struct BlockEval {
         }
         if (threadIdx.x == 0) C->S->lm_blocks += ntot;
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-        double *av = reinterpret_cast<double *>(&a);
+        // warp reduce-scatter of the 78 sums (padded to 80): every step halves the number of values a lane carries
+        // (80 -> 40 -> 20 -> 10 -> 5) and the partner distance; 80 shuffled doubles instead of 78 x 5 for butterflies
+        {
+            const double *av = reinterpret_cast<const double *>(&a);
+            double v[80];
 #pragma unroll
-        for (int v = 0; v < LM_ACC_DOUBLES; v++) {
-            double s = av[v];
+            for (int i = 0; i < 80; i++) v[i] = i < LM_ACC_DOUBLES ? av[i] : 0.0;
+#define MP_RS_STEP(H_, BIT_) \
+            { const bool up = (lane & BIT_) != 0; \
+              _Pragma("unroll") for (int i = 0; i < H_; i++) { \
+                  const double keep = up ? v[H_ + i] : v[i], send = up ? v[i] : v[H_ + i]; \
+                  v[i] = keep + __shfl_xor_sync(0xffffffffu, send, BIT_); } }
+            MP_RS_STEP(40, 16) MP_RS_STEP(20, 8) MP_RS_STEP(10, 4) MP_RS_STEP(5, 2)
+#undef MP_RS_STEP
+            const int g0 = ((lane >> 4) & 1) * 40 + ((lane >> 3) & 1) * 20 + ((lane >> 2) & 1) * 10 + ((lane >> 1) & 1) * 5;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) sh->part[warp][v] = s;
+            for (int i = 0; i < 5; i++) {
+                const double s = v[i] + __shfl_xor_sync(0xffffffffu, v[i], 1);
+                if ((lane & 1) == 0 && g0 + i < LM_ACC_DOUBLES) sh->part[warp][g0 + i] = s;
+            }
         }
         __syncthreads();
         for (int v = threadIdx.x; v < LM_ACC_DOUBLES; v += blockDim.x) { // any CTA size
