@@ -132,7 +132,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.lo_req = A.lo_req.as<int>();
     L.gsz = gsz;
     L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>());
-    MP_CUDA(cudaMemsetAsync(L.clk, 0, 64, s));
+    MP_CUDA(cudaMemsetAsync(L.clk, 0, 128, s));
     const LoopParams *dprm = A.prm.as<LoopParams>();
     MP_CUDA(cudaEventRecord(c->ev[1], s));
     init_state_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, dprm);
@@ -264,7 +264,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaEventRecord(c->ev[2], s));
     MP_CUDA(cudaMemcpyAsync(out_models, A.out_models.p, n_pairs * sizeof(mp_model), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(out_stats, A.out_stats.p, n_pairs * sizeof(mp_stats), cudaMemcpyDeviceToHost, s));
-    MP_CUDA(cudaMemcpyAsync(c->phase_clk, L.clk, 64, cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(c->phase_clk, L.clk, 128, cudaMemcpyDeviceToHost, s));
     c->last_groups = G;
     if (out_inliers && N > 0)
         MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, 3 * (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -274,6 +274,10 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaEventElapsedTime(&k, c->ev[1], c->ev[2]));
     MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));
     c->last_kernel_ms = k; c->last_total_ms = t; c->last_launches = launches;
+    if (trace) {
+        const char *nm[8] = {"feed", "propose:setup", "cholesky", "forward", "backward", "model-change", "plus", "first"};
+        for (int i = 0; i < 8; i++) fprintf(stderr, "[mp] LM driver %-14s %8.3f Gcycles\n", nm[i], c->phase_clk[8 + i] / 1e9);
+    }
     c->last_rounds = (int)rounds;
     for (int i = 0; i < 4; i++) { c->class_ms[i] = 0; c->class_launches[i] = 0; }
     for (int i = 0; i + 1 < c->n_tick; i++) {

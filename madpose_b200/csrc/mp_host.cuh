@@ -72,7 +72,7 @@ struct mp_ctx {
     std::vector<cudaEvent_t> tick_ev;
     std::vector<int> tick_cls;
     int n_tick = 0;
-    unsigned long long phase_clk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long phase_clk[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     int groups_override = 0, last_groups = 1; // 0 = automatic

@@ -292,7 +292,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
         atomicExch(&L.st[p].phase, final_phase);
         if (final_phase == PH_DONE) {
             atomicSub(L.n_active + p / L.gsz, 1);
-            for (int q = 0; q < 8; q++) atomicAdd(L.clk + q, S.clk[q]);
+            for (int q = 0; q < 16; q++) atomicAdd(L.clk + q, S.clk[q]);
         }
     }
 }
@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lm_batch_kernel(co
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     const int j = blockIdx.x;
-    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; S.lm_blocks = 0; for (int q = 0; q < 8; q++) S.clk[q] = 0; sh.m_tmp = start[j]; }
+    if (threadIdx.x == 0) { S.lm_solves = 0; S.lm_iters = 0; S.lm_blocks = 0; for (int q = 0; q < 16; q++) S.clk[q] = 0; sh.m_tmp = start[j]; }
     __syncthreads();
     BlockCtx C;
     C.pc = pcp; C.M = M + pcp->off; C.prm = prmp; C.S = &S; C.rngB = nullptr; C.sh = &sh; C.cap = 0;

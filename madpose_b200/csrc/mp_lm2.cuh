@@ -74,7 +74,13 @@ MP_HD void lm_plus(const LmSetup &L, const double *x, const double *d, double *x
     xp[10] += dv[9]; xp[11] += dv[10];
     const double n = sqrt(dv[1] * dv[1] + dv[2] * dv[2] + dv[3] * dv[3]);
     if (n > 0) {
+#ifdef __CUDA_ARCH__
+        double sv, e0;
+        sincos(n, &sv, &e0); // one argument reduction for both
+        const double sn = sv / n, e1 = sn * dv[1], e2 = sn * dv[2], e3 = sn * dv[3];
+#else
         const double sn = sin(n) / n, e0 = cos(n), e1 = sn * dv[1], e2 = sn * dv[2], e3 = sn * dv[3];
+#endif
         const double *q = x + 1;
         xp[1] = e0 * q[0] - e1 * q[1] - e2 * q[2] - e3 * q[3];
         xp[2] = e0 * q[1] + e1 * q[0] + e2 * q[3] - e3 * q[2];
@@ -111,6 +117,7 @@ struct LmDriver {
     double cost, radius, decrease, mcc;
     double min_cost, cur_cost, ref_cost, cand_cost, acc_ref, acc_cand;
     int n_nonmono, n_invalid, it;
+    unsigned long long prof[8]; // device profiling aid (mp_lm_warp.cuh): cycles per driver section
 
     MP_HD double grad_max(const double *xx, const double *gg) const {
         double d[LM_NT], xp[LM_NA], mx = 0;

@@ -1,10 +1,12 @@
 // K5 (part 3) -- the LM driver of mp_lm2.cuh executed by ONE WARP instead of one thread.
-// Same state (an LmDriver in shared memory), same arithmetic per element and the same order of
-// every floating-point sum as the scalar driver (so both produce identical bits); what changes
-// is who does it: the 11 x 11 systems are spread over the lanes (lane = row), the Cholesky
-// factorisation is right-looking with the rows in registers and the pivot column broadcast by
-// shuffles, the forward substitution is column-oriented.  Scalar decisions are taken by lane 0
-// and broadcast.  All 32 lanes of the warp must call these functions together.
+// Same state (an LmDriver in shared memory) and the same algorithm as the scalar driver; what
+// changes is who does it and the form of the elimination: the 11 x 11 systems are spread over
+// the lanes (lane = row), the damped normal equations are factored as L D L^T (right-looking,
+// rows in registers, pivot column broadcast by shuffles: no square roots, one reciprocal per
+// pivot, substitutions without divisions) and the model cost change uses A y = -g - D y.  The
+// scalar driver (L L^T, mp_lm2.cuh) is what the host check compiles against the oracle; the two
+// agree to rounding (the GPU LM tests hold both to the oracle within 1e-8).  Scalar decisions are
+// taken by lane 0 and broadcast.  All 32 lanes of the warp must call these functions together.
 #pragma once
 
 namespace mp {
@@ -29,8 +31,11 @@ __device__ __forceinline__ void warp_compress(const LmSetup &L, const double *to
 }
 
 // LmDriver::first
+#define LMW_T0() long long lmw_t_ = clock64()
+#define LMW_T(slot_) do { if (lane == 0) { const long long n_ = clock64(); d.prof[slot_] += (unsigned long long)(n_ - lmw_t_); lmw_t_ = n_; } } while (0)
 __device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
+    LMW_T0();
     const int nt = L.nt;
     warp_compress(L, tot, d.A, d.g, lane);
     if (lane < nt) d.scale[lane] = 1.0 / (1.0 + sqrt(d.A[lane * nt + lane]));
@@ -51,6 +56,7 @@ __device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     }
     go = __shfl_sync(LMW_FULL, go, 0);
     __syncwarp();
+    LMW_T(7);
     return go != 0;
 }
 
@@ -72,6 +78,7 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
         stop = __shfl_sync(LMW_FULL, stop, 0);
         if (stop) return false;
         __syncwarp();
+        LMW_T0();
         const double radius = d.radius;
         const bool rowl = lane < nt;
         const int rl = rowl ? lane : 0; // idle lanes shadow row 0 (their results are never read)
@@ -100,21 +107,27 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
                 if (b == rl) row[b] += add;
         }
         __syncwarp();
-        // right-looking Cholesky, no early exit: after step k, row[k] = L[lane][k]; a bad pivot is remembered
+        LMW_T(1);
+        // right-looking LDL^T, no square roots and ONE division per pivot (the reciprocal, computed by every lane):
+        // after step k, row[k] = l_ik on lanes i > k; pivots d_k > 0 <=> the scalar driver's Cholesky succeeds.
+        // (The scalar driver of mp_lm2.cuh uses L L^T; the two agree to rounding, ~1e-16 relative in the step.)
         bool bad = false;
+        double rinv[LM_NT];
 #pragma unroll
         for (int k = 0; k < LM_NT; k++) {
+            rinv[k] = 0.0;
             if (LMW_IN(k)) {
                 const double dk = __shfl_sync(LMW_FULL, row[k], k);
                 bad = bad || !(dk > 0.0) || !finite_d(dk);
-                const double lkk = sqrt(dk);
-                const double lik = lane == k ? lkk : row[k] / lkk;
-                row[k] = lik;
+                const double rk = 1.0 / dk;
+                rinv[k] = rk;
+                const double aik = row[k], lik = aik * rk; // a_ik = l_ik d_k
+                if (lane != k) row[k] = lik;
 #pragma unroll
                 for (int j = k + 1; j < LM_NT; j++) {
                     if (LMW_IN(j)) {
-                        const double ljk = __shfl_sync(LMW_FULL, lik, j);
-                        if (j <= lane) row[j] -= lik * ljk;
+                        const double ajk = __shfl_sync(LMW_FULL, aik, j);
+                        if (j <= lane) row[j] -= lik * ajk; // a_ij -= l_ik d_k l_jk
                     }
                 }
             }
@@ -122,53 +135,55 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
         if (rowl) {
 #pragma unroll
             for (int j = 0; j < LM_NT; j++)
-                if (j <= lane) d.Lc[lane * nt + j] = row[j];
+                if (j < lane) d.Lc[lane * nt + j] = row[j]; // strictly lower part: the unit-triangular factor
         }
-        // forward substitution, column-oriented: y_k known -> every later row subtracts L[i][k] y_k
+        LMW_T(2);
+        // forward substitution with the unit lower factor (column-oriented), then the diagonal
         {
             double s = gsl;
 #pragma unroll
             for (int k = 0; k < LM_NT; k++) {
                 if (LMW_IN(k)) {
-                    const double yk = __shfl_sync(LMW_FULL, s / row[k], k);
-                    if (lane == k) d.yw[k] = yk;
+                    const double yk = __shfl_sync(LMW_FULL, s, k);
+                    if (lane == k) d.yw[k] = yk * rinv[k];
                     if (lane > k) s -= row[k] * yk;
                 }
             }
         }
         __syncwarp();
-        // back substitution (every lane, redundantly; sums in the scalar order k = i+1 .. nt-1)
+        LMW_T(3);
+        // back substitution with the unit upper factor (every lane, redundantly): FMAs only
         double xs[LM_NT];
         bool ok = !bad;
 #pragma unroll
         for (int i = LM_NT - 1; i >= 0; i--) {
             double v = 0.0;
             if (LMW_IN(i)) {
-                double t = d.yw[i];
+                v = d.yw[i];
 #pragma unroll
                 for (int k = i + 1; k < LM_NT; k++)
-                    if (LMW_IN(k)) t -= d.Lc[k * nt + i] * xs[k];
-                v = t / d.Lc[i * nt + i];
+                    if (LMW_IN(k)) v -= d.Lc[k * nt + i] * xs[k];
                 ok = ok && finite_d(v);
             }
             xs[i] = v;
         }
+        LMW_T(4);
+        // model cost change -(g.y + y.A y / 2) with A y = -g - D y (y solves the damped system): 2 x nt terms
         double mcc = 0;
         if (ok) {
-            double dg = 0, dAd = 0;
+            double dg = 0, dDd = 0;
 #pragma unroll
             for (int a = 0; a < LM_NT; a++) xs[a] = -xs[a];
 #pragma unroll
             for (int a = 0; a < LM_NT; a++) {
                 if (LMW_IN(a)) {
                     dg += xs[a] * d.gs[a];
-#pragma unroll
-                    for (int b = 0; b < LM_NT; b++)
-                        if (LMW_IN(b)) dAd += xs[a] * d.As[a * nt + b] * xs[b];
+                    dDd += xs[a] * xs[a] * (fmin(fmax(d.As[a * nt + a], 1e-6), 1e32) / radius);
                 }
             }
-            mcc = -(dg + 0.5 * dAd);
+            mcc = 0.5 * (dDd - dg);
         }
+        LMW_T(5);
         if (!ok || !(mcc > 0)) {
             int fail_ = 0;
             if (lane == 0) {
@@ -192,6 +207,7 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
             lm_plus(L, d.x, dd, d.xc);
         }
         __syncwarp();
+        LMW_T(6);
         return true;
     }
 #undef LMW_IN
@@ -206,6 +222,7 @@ template <int NTK> __device__ __forceinline__ bool warp_lm_propose(LmDriver &d, 
 __device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
     const int nt = L.nt;
+    LMW_T0();
     warp_compress(L, tot, d.An, d.gn, lane);
     int verdict = 0; // 0 finished, 1 rejected step (continue), 2 accepted step
     double cc = 0, rel = 0;
@@ -242,6 +259,7 @@ __device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
         verdict = __shfl_sync(LMW_FULL, verdict, 0);
     }
     __syncwarp();
+    LMW_T(0);
     return verdict != 0;
 }
 

@@ -50,7 +50,7 @@ struct alignas(128) PairState { // 128-byte aligned: no cache line is shared bet
     unsigned long long evals64, lm_blocks; // fp64 (model x match) evaluations; LM residual-block evaluations
     unsigned lm_solves, lm_iters;
     int sizes[2][3], non_min_sample_size, min_sample_size;
-    unsigned long long clk[8]; // SM-clock cycles of thread 0 per phase: 0 scan 1 inliers 2 score64 3 lm eval 4 lm driver 5 shuffle 6 unflatten 7 LO total
+    unsigned long long clk[16]; // SM-clock cycles of thread 0 per phase: 0 scan 1 inliers 2 score64 3 lm eval 4 lm driver 5 shuffle 6 unflatten 7 LO total
 };
 
 // per-pair work buffers of one round

@@ -37,7 +37,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
     S.number_lo = 0; S.best_num_inliers = 0;
     for (int t = 0; t < 3; t++) { S.num_inl[t] = 0; S.ratios[t] = 0; }
     S.hyps_scored = 0; S.evals = 0; S.evals64 = 0; S.lm_blocks = 0; S.lm_solves = 0; S.lm_iters = 0;
-    for (int q = 0; q < 8; q++) S.clk[q] = 0;
+    for (int q = 0; q < 16; q++) S.clk[q] = 0;
     mt_seed(&L.rngA[p], prm.opt.random_seed);
     mt_seed(&L.rngB[p], prm.opt.random_seed);
     L.lo_req[p] = 0; L.wk[p].blen = 0;

@@ -107,6 +107,7 @@ template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, con
         double x0[LM_NA];
         lm_model_to_x(start, x0);
         sh->lm_go = drv.begin(&L, x0) ? 1 : 0;
+        for (int q = 0; q < 8; q++) drv.prof[q] = 0;
         for (int k = 0; k < LM_NA; k++) sh->lm_x[k] = drv.x[k];
     }
     __syncthreads();
@@ -135,6 +136,7 @@ template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, con
         lm_x_to_model(KIND, drv.x, &m);
         *out = m;
         *info_out = drv.info;
+        for (int q = 0; q < 8; q++) C.S->clk[8 + q] += drv.prof[q];
     }
     __syncthreads();
     MP_CLK_END(C, 4);
