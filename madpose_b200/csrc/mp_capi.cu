@@ -1,6 +1,9 @@
 // C ABI of madpose_b200 (include/madpose_b200.h).  Every entry point runs CUDA
 // kernels on the context's device; there is no CPU fallback.
 #include <cstdlib>
+#include <thread>
+#include <vector>
+#include <algorithm>
 #include "mp_host.cuh"
 #include "mp_kernels.cuh"
 #include "mp_estimate.cuh"
@@ -36,19 +39,39 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
     MP_CUDA(c->d_m64.reserve((size_t)(N > 0 ? N : 1) * sizeof(Match64)));
     MP_CUDA(c->d_s32.reserve((size_t)c->total32 * sizeof(float4)));
     PairRaw *raw = c->h_raw.as<PairRaw>();
-    for (int p = 0; p < n_pairs; p++) {
-        const mp_pair &q = pairs[p];
-        size_t n = q.n;
-        std::memcpy(c->h_x0.as<double>() + 2 * c->off[p], q.x0, 2 * n * sizeof(double));
-        std::memcpy(c->h_x1.as<double>() + 2 * c->off[p], q.x1, 2 * n * sizeof(double));
-        std::memcpy(c->h_d0.as<double>() + c->off[p], q.d0, n * sizeof(double));
-        std::memcpy(c->h_d1.as<double>() + c->off[p], q.d1, n * sizeof(double));
-        PairRaw &r = raw[p];
-        r.n = q.n; r.kind = kind; r.off = c->off[p]; r.off32 = c->off32[p];
-        std::memcpy(r.K0, q.K0, sizeof(r.K0)); std::memcpy(r.K1, q.K1, sizeof(r.K1));
-        for (int k = 0; k < 2; k++) {
-            r.pp0[k] = q.pp0[k]; r.pp1[k] = q.pp1[k]; r.min_depth[k] = q.min_depth[k];
-            r.thr[k] = opt->squared_inlier_thresholds[k]; r.w[k] = opt->data_type_weights[k];
+    auto pack_range = [&](int p0, int p1) {
+        for (int p = p0; p < p1; p++) {
+            const mp_pair &q = pairs[p];
+            size_t n = q.n;
+            std::memcpy(c->h_x0.as<double>() + 2 * c->off[p], q.x0, 2 * n * sizeof(double));
+            std::memcpy(c->h_x1.as<double>() + 2 * c->off[p], q.x1, 2 * n * sizeof(double));
+            std::memcpy(c->h_d0.as<double>() + c->off[p], q.d0, n * sizeof(double));
+            std::memcpy(c->h_d1.as<double>() + c->off[p], q.d1, n * sizeof(double));
+            PairRaw &r = raw[p];
+            r.n = q.n; r.kind = kind; r.off = c->off[p]; r.off32 = c->off32[p];
+            std::memcpy(r.K0, q.K0, sizeof(r.K0)); std::memcpy(r.K1, q.K1, sizeof(r.K1));
+            for (int k = 0; k < 2; k++) {
+                r.pp0[k] = q.pp0[k]; r.pp1[k] = q.pp1[k]; r.min_depth[k] = q.min_depth[k];
+                r.thr[k] = opt->squared_inlier_thresholds[k]; r.w[k] = opt->data_type_weights[k];
+            }
+        }
+    };
+    { // the caller's arrays are pageable and scattered: pack them into the pinned staging buffers on several threads
+        int nt = (int)std::min<long long>(8, std::max<long long>(1, N / 200000));
+        nt = std::min<int>(nt, std::max(1u, std::thread::hardware_concurrency()));
+        if (nt <= 1) pack_range(0, n_pairs);
+        else {
+            std::vector<std::thread> th;
+            int p0 = 0;
+            for (int t = 0; t < nt; t++) { // equal shares of matches
+                int p1 = p0;
+                const long long want = N * (t + 1) / nt;
+                while (p1 < n_pairs && c->off[p1 + 1] <= want) p1++;
+                if (t == nt - 1) p1 = n_pairs;
+                th.emplace_back(pack_range, p0, p1);
+                p0 = p1;
+            }
+            for (auto &x : th) x.join();
         }
     }
     cudaStream_t s = c->stream;

@@ -105,6 +105,7 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
 #pragma unroll
             for (int b = 0; b < LM_NT; b++)
                 if (b == rl) row[b] += add;
+            if (rowl) d.Ad[lane] = add; // the damping D_aa, for the model cost change below
         }
         __syncwarp();
         LMW_T(1);
@@ -178,7 +179,7 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
             for (int a = 0; a < LM_NT; a++) {
                 if (LMW_IN(a)) {
                     dg += xs[a] * d.gs[a];
-                    dDd += xs[a] * xs[a] * (fmin(fmax(d.As[a * nt + a], 1e-6), 1e32) / radius);
+                    dDd += xs[a] * xs[a] * d.Ad[a];
                 }
             }
             mcc = 0.5 * (dDd - dg);
