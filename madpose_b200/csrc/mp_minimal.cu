@@ -5,7 +5,7 @@
 #include "mp_minimal.cuh"
 
 #ifndef MP_MIN_CTAS
-#define MP_MIN_CTAS 8
+#define MP_MIN_CTAS 12
 #endif
 namespace mp {
 
