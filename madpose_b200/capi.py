@@ -225,15 +225,18 @@ class Context:
                                          info.ctypes.data_as(C.c_void_p)))
         return out, info
 
-    def estimate_batch(self, kind, pairs, opt, cfg):
-        """pairs: list of Pair.  Returns (models (P,17), list of Stats, list of 3 inlier index arrays per pair)."""
+    def estimate_batch(self, kind, pairs, opt, cfg, split=True):
+        """pairs: list of Pair (or a ready `(Pair * n)` array).  Returns (models (P,17), list of Stats, list of 3 inlier
+        index arrays per pair); split=False returns the flat inlier buffer of the C ABI instead (no per-pair copies)."""
         n = len(pairs)
-        arr = (Pair * n)(*pairs)
-        models = np.zeros((n, MODEL_DOUBLES)); stats = (Stats * n)()
+        arr = pairs if isinstance(pairs, C.Array) else (Pair * n)(*pairs)
+        models = np.empty((n, MODEL_DOUBLES)); stats = (Stats * n)()
         tot = sum(p.n for p in pairs)
-        inl = np.zeros(3 * tot + 1, np.int32)
+        inl = np.empty(3 * tot + 1, np.int32)
         self._check(self.lib.mp_estimate_batch(self.ctx, kind, n, arr, C.byref(opt), C.byref(cfg),
                                                models.ctypes.data_as(C.c_void_p), stats, inl.ctypes.data_as(C.c_void_p)))
+        if not split:
+            return models, stats, inl
         out, o = [], 0
         for p, s in zip(pairs, stats):
             out.append([inl[o + t * p.n: o + t * p.n + s.num_inliers[t]].copy() for t in range(3)])

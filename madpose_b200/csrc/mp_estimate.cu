@@ -83,7 +83,12 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.h_active.reserve(4 * MP_MAX_GROUPS));
     LoopParams *prm = A.h_prm.as<LoopParams>();
-    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BMAX; prm->guard = 1e-3;
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BMAX;
+    {
+        const char *e = getenv("MP_B_AFTER_LO"); // experiments
+        const int v = e ? atoi(e) : 0;
+        prm->b_after_lo = v > 0 ? std::min(v, prm->bmax) : prm->bmax; // measured on configs[1]: 16 -> 245 ms, 32 -> 235, 64 -> 232
+    } prm->guard = 1e-3;
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
     // waits for them: a pair inside a local optimisation sits the rounds out until its lo_kernel publishes it again.
@@ -310,7 +315,7 @@ int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt,
     MP_CUDA(A.prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     LoopParams *prm = A.h_prm.as<LoopParams>();
-    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = 1; prm->bmax = LP_BMAX; prm->guard = 1e-3;
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = 1; prm->bmax = LP_BMAX; prm->b_after_lo = LP_BMAX / 4; prm->guard = 1e-3;
     MP_CUDA(c->d_models.reserve(2 * (size_t)n_problems * sizeof(Model)));
     MP_CUDA(c->d_idx.reserve(((size_t)nidx + 3 * (size_t)n_problems + 8) * sizeof(int)));
     MP_CUDA(c->d_scores64.reserve(4 * (size_t)n_problems * sizeof(double)));

@@ -169,7 +169,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
                 }
                 S.B = min(prm.bmax, S.B * 2);
             }
-        } else if (lo_event && threadIdx.x == 0) S.B = max(4, prm.bmax / 4);
+        } else if (lo_event && threadIdx.x == 0) S.B = prm.b_after_lo;
         if (threadIdx.x == 0) S.clk[0] += (unsigned long long)(clock64() - scan_t0);
         __syncthreads();
     }

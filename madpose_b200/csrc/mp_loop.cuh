@@ -31,6 +31,7 @@ struct LoopParams {
     mp_options opt;
     mp_config cfg;
     int n_pairs, bmax;
+    int b_after_lo; // batch length of the first round after a local optimisation (doubles every round up to bmax)
     double guard; // relative guard band of the fp32 score filter
 };
 
@@ -115,8 +116,11 @@ static __device__ __noinline__ double block_score64(const PairConst &pc, const M
 //   pass 2  ranks = prefix + popc(ballot below my lane) -> ordered, conflict-free stores
 constexpr int INL_CH = 16, INL_MAXW = 8;
 struct InlScratch { int cnt[3][INL_CH * INL_MAXW]; int base[3]; };
+// score_out != nullptr: the same pass also returns ScoreModel(model) (hybrid_ransac.h:265-282) -- same residuals, same
+// per-thread order of the sum and the same block_sum tree as block_score64, hence the same bits.
 static __device__ __noinline__ void block_inliers(const PairConst &pc, const Match64 *m, const Model &model,
-                                           const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16]) {
+                                           const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16],
+                                           double *score_out = nullptr, int score_type = 0, double *red = nullptr) {
     __shared__ InlScratch isc;
     Eval64 e;
     make_eval64(pc, model, &e);
@@ -126,6 +130,7 @@ static __device__ __noinline__ void block_inliers(const PairConst &pc, const Mat
     __syncthreads();
     if (threadIdx.x < 3) isc.base[threadIdx.x] = 0;
     __syncthreads();
+    double acc = 0;
     for (int sbase = 0; sbase < n; sbase += INL_CH * blockDim.x) {
         unsigned long long flags = 0;
 #pragma unroll 4
@@ -134,7 +139,13 @@ static __device__ __noinline__ void block_inliers(const PairConst &pc, const Mat
             unsigned f = 0;
             if (i < n) {
                 const Match64 mm = m[i];
-                f = (eval64(e, mm, 0) < t0 ? 1u : 0u) | (eval64(e, mm, 1) < t1 ? 2u : 0u) | (eval64(e, mm, 2) < t2 ? 4u : 0u);
+                const double r0 = eval64(e, mm, 0), r1 = eval64(e, mm, 1), r2 = eval64(e, mm, 2);
+                f = (r0 < t0 ? 1u : 0u) | (r1 < t1 ? 2u : 0u) | (r2 < t2 ? 4u : 0u);
+                if (score_out) {
+                    const double s0 = score_type == 1 ? DBL_MAX : r0, s1 = score_type == 1 ? DBL_MAX : r1,
+                                 s2 = score_type == 2 ? DBL_MAX : r2;
+                    acc += pc.w[0] * msac64(s0, pc.thr[0]) + pc.w[1] * msac64(s1, pc.thr[1]) + pc.w[2] * msac64(s2, pc.thr[2]);
+                }
             }
             flags |= (unsigned long long)f << (3 * c);
             const unsigned b0 = __ballot_sync(0xffffffffu, f & 1u), b1 = __ballot_sync(0xffffffffu, f & 2u),
@@ -177,6 +188,11 @@ static __device__ __noinline__ void block_inliers(const PairConst &pc, const Mat
     }
     if (threadIdx.x < 3) cnt_sh[threadIdx.x] = isc.base[threadIdx.x];
     __syncthreads();
+    if (score_out) {
+        const double sc = block_sum(acc, red);
+        if (threadIdx.x == 0) *score_out = sc;
+        __syncthreads();
+    }
 }
 
 // utils::NumRequiredIterations (ext/RansacLib/RansacLib/utils.h:142-178), vector form

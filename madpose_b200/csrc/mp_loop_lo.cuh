@@ -322,11 +322,12 @@ static __device__ __noinline__ void block_unflatten(const BlockCtx &C, const int
 }
 
 // LeastSquaresFit (hybrid_ransac.h:484-538)
+// have_inliers: inl_cur / sh->cnt already hold GetInliers(*m, thr) (block_score_inliers ran on the same model)
 template <int KIND> __device__ __noinline__ void block_lsq_fit(const BlockCtx &C, const double *thr, int solver, Model *m,
-                                                  bool all_inliers) {
+                                                  bool all_inliers, bool have_inliers = false) {
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;
-    { MP_CLK_BEGIN(); block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
+    if (!have_inliers) { MP_CLK_BEGIN(); block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
     if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     const int *sz = C.S->sizes[solver];
@@ -358,6 +359,18 @@ __device__ inline double block_score_counted(const BlockCtx &C, const Model &m) 
     return s;
 }
 
+// ScoreModel(m) and GetInliers(m, thr_inl) in ONE pass over the matches (the reference calls them back to back on the
+// same model all through LocalOptimization); inliers are left in inl_cur / sh->cnt for the next block_lsq_fit.
+// The work counters count both, as the reference evaluates both.
+__device__ inline double block_score_inliers(const BlockCtx &C, const Model &m, const double *thr_inl) {
+    MP_CLK_BEGIN();
+    __shared__ double sc_sh;
+    block_inliers(*C.pc, C.M, m, thr_inl, C.inl_cur, C.sh->cnt, C.sh->wcnt, &sc_sh, C.prm->cfg.score_type, C.sh->red);
+    MP_CLK_END(C, 1);
+    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; }
+    return sc_sh;
+}
+
 // LocalOptimization (hybrid_ransac.h:383-482).  best / best_score / best_solver live in shared memory.
 template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, int solver, Model *best,
                                                              double *best_score, int *best_solver) {
@@ -380,10 +393,9 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
     if (threadIdx.x == 0) sh->m_init = *best;
     __syncthreads();
     block_lsq_fit<KIND>(C, thr, solver, &sh->m_init, true);
-    double sc = block_score_counted(C, sh->m_init);
+    // score of m_init + its base inliers at the nominal thresholds (flattened below with type offsets)
+    double sc = block_score_inliers(C, sh->m_init, pc.thr);
     update_best(sc, &sh->m_init);
-    // base inliers of m_init at the nominal thresholds, flattened with type offsets
-    { MP_CLK_BEGIN(); block_inliers(pc, C.M, sh->m_init, pc.thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
     if (threadIdx.x == 0) C.S->evals64 += n;
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
@@ -413,15 +425,16 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
         if (threadIdx.x == 0) sh->m_lo = sh->m_init;
         __syncthreads();
         block_lsq<KIND>(C, l0, s0, l1, s1, l2, s2, &sh->m_lo);
-        sc = block_score_counted(C, sh->m_lo);
+        sc = block_score_inliers(C, sh->m_lo, pc.thr); // the inliers feed the fit below
         update_best(sc, &sh->m_lo);
-        block_lsq_fit<KIND>(C, pc.thr, solver, &sh->m_lo, false);
+        block_lsq_fit<KIND>(C, pc.thr, solver, &sh->m_lo, false, true);
         double cur[3] = {thr[0], thr[1], thr[2]};
         for (int i = 0; i < o.num_lsq_iterations; ++i) {
-            block_lsq_fit<KIND>(C, cur, solver, &sh->m_lo, false);
-            sc = block_score_counted(C, sh->m_lo);
-            update_best(sc, &sh->m_lo);
+            block_lsq_fit<KIND>(C, cur, solver, &sh->m_lo, false, i > 0);
             for (int t = 0; t < 3; t++) cur[t] -= step[t];
+            if (i + 1 < o.num_lsq_iterations) sc = block_score_inliers(C, sh->m_lo, cur); // inliers at the next thresholds
+            else sc = block_score_counted(C, sh->m_lo);
+            update_best(sc, &sh->m_lo);
         }
     }
     __syncthreads();
