@@ -25,19 +25,28 @@ template <int KIND> MP_HD int minimal_affine(const PairConst &pc, const Match64 
     if (KIND == CALIB) ns = affine_calibrated(x0, x1, d0, d1, sols);
     else if (KIND == SHARED) ns = affine_shared_focal(x0, x1, d0, d1, sols);
     else ns = affine_two_focal(x0, x1, d0, d1, sols);
-    int n = 0;
+    // pass 1 (cheap): solutions whose corrected depths are all positive (solver.cpp:503,702,1006), compacted in order,
+    // so that the expensive part below runs over lists of similar length in every lane of a warp
+    int keep[8], nk = 0;
     for (int q = 0; q < ns; q++) {
         const AffSol &s = sols[q];
-        double X[NPT][3], Y[NPT][3];
         bool pos = true;
+        for (int k = 0; k < NPT; k++) {
+            const double e1 = d0[k] + s.b1, e2 = d1[k] * s.a2 + s.b2 * s.a2;
+            if (e1 <= 0 || e2 <= 0) pos = false;
+        }
+        if (pos) keep[nk++] = q;
+    }
+    int n = 0;
+    for (int qq = 0; qq < nk; qq++) {
+        const AffSol &s = sols[keep[qq]];
+        double X[NPT][3], Y[NPT][3];
         const double fa = KIND == CALIB ? 1.0 : s.f1, fb = KIND == CALIB ? 1.0 : s.f2;
         for (int k = 0; k < NPT; k++) {
             const double e1 = d0[k] + s.b1, e2 = d1[k] * s.a2 + s.b2 * s.a2;
-            if (e1 <= 0 || e2 <= 0) pos = false; // solver.cpp:503,702,1006
             X[k][0] = x0[k][0] / fa * e1; X[k][1] = x0[k][1] / fa * e1; X[k][2] = x0[k][2] * e1;
             Y[k][0] = x1[k][0] / fb * e2; Y[k][1] = x1[k][1] / fb * e2; Y[k][2] = x1[k][2] * e2;
         }
-        if (!pos) continue;
         Model m;
         if (!kabsch<NPT>(X, Y, m.R, m.t)) continue;
         m.scale = s.a2; m.o0 = s.b1; m.o1 = s.b2 * s.a2; m.f0 = fa; m.f1 = fb;

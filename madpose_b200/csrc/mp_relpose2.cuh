@@ -143,11 +143,16 @@ MP_HD int relpose_6pt_shared_focal(const double (*x1)[3], const double (*x2)[3],
         }
         coef[j] = s / 16.0;
     }
-    const int nr = real_roots<15>(coef, 15, roots);
+    int nr = real_roots<15>(coef, 15, roots);
+    { // keep the admissible roots (w = 1 / f^2 > 0) only, in order: the lanes of a warp then walk lists of similar length
+        int k = 0;
+        for (int q = 0; q < nr; q++)
+            if (roots[q] > 0) roots[k++] = roots[q];
+        nr = k;
+    }
     int n = 0;
     for (int q = 0; q < nr && n < 15; q++) {
         const double wr = roots[q];
-        if (!(wr > 0)) continue;
         // null vector of C(w): elimination with full pivoting, free variable = 1
         double M[100];
         int cp[10];
