@@ -23,6 +23,25 @@ MP_HD double poly_val_d(const double *p, int n, double x, double *dp) {
     return r;
 }
 
+// The same two evaluations on a coefficient array padded with zeros up to degree MAXD, fully unrolled: the
+// coefficients stay in registers (static indexing) and the leading zeros change nothing (fma(0, x, c) == c).
+template <int MAXD> MP_HD double poly_val_pad(const double (&p)[MAXD + 1], double x) {
+    double r = p[MAXD];
+#pragma unroll
+    for (int i = MAXD - 1; i >= 0; i--) r = fma(r, x, p[i]);
+    return r;
+}
+template <int MAXD> MP_HD double poly_val_d_pad(const double (&p)[MAXD + 1], double x, double *dp) {
+    double r = 0, d = 0;
+#pragma unroll
+    for (int i = MAXD; i >= 0; i--) {
+        d = fma(d, x, r);
+        r = fma(r, x, p[i]);
+    }
+    *dp = d;
+    return r;
+}
+
 template <int MAXD> struct Sturm {
     double c[MAXD + 1][MAXD + 1]; // chain polynomials
     int deg[MAXD + 1];
@@ -106,22 +125,25 @@ template <int MAXD> MP_HD int real_roots_unscaled(const double *pin, int n, doub
         if (cm - chi > 0 && sp < MAXD + 2) { lo_s[sp] = mid; hi_s[sp] = ihi; cl_s[sp] = cm; ch_s[sp] = chi; sp++; }
         if (clo - cm > 0 && sp < MAXD + 2) { lo_s[sp] = ilo; hi_s[sp] = mid; cl_s[sp] = clo; ch_s[sp] = cm; sp++; }
     }
-    // phase 2: refinement of every isolated interval (bisection, then Newton)
+    // phase 2: refinement of every isolated interval (bisection, then Newton) on a register copy of p
+    double pp[MAXD + 1];
+#pragma unroll
+    for (int i = 0; i <= MAXD; i++) pp[i] = i <= n ? p[i] : 0.0;
     for (int r = 0; r < nq; r++) {
         const double ilo = qlo[r], ihi = qhi[r];
-        double lo = ilo, hi = ihi, flo = poly_val(p, n, lo), fhi = poly_val(p, n, hi);
+        double lo = ilo, hi = ihi, flo = poly_val_pad<MAXD>(pp, lo), fhi = poly_val_pad<MAXD>(pp, hi);
         double x = 0.5 * (lo + hi);
         if (flo * fhi <= 0) {
             for (int it = 0; it < 200 && hi - lo > 1e-15 * (1.0 + fabs(x)); it++) {
                 x = 0.5 * (lo + hi);
-                double fx = poly_val(p, n, x);
+                double fx = poly_val_pad<MAXD>(pp, x);
                 if (fx == 0.0) break;
                 if ((fx < 0) == (flo < 0)) { lo = x; flo = fx; } else hi = x;
             }
             x = 0.5 * (lo + hi);
         }
         for (int it = 0; it < 8; it++) {
-            double d, f = poly_val_d(p, n, x, &d);
+            double d, f = poly_val_d_pad<MAXD>(pp, x, &d);
             if (d == 0.0) break;
             double xn = x - f / d;
             if (!(xn >= ilo && xn <= ihi)) break;
