@@ -41,13 +41,17 @@ MP_HD uint32_t mt_temper(uint32_t y) {
 // (a no-op functor for a single thread).
 template <class Sync> MP_HD void mt_refill(MtStream *s, int lane, int nlanes, Sync sync) {
     const unsigned long long g = s->gen;
+    const unsigned gb = (unsigned)(g % MT_RING); // ring slot of raw word g; all other slots by 32-bit add + one wrap
+    auto slot = [gb](int off) { // ring slot of raw word g + off, -MT_N <= off < MT_N
+        unsigned r = gb + (unsigned)(off + MT_RING);
+        if (r >= 2u * MT_RING) r -= 2u * MT_RING;
+        else if (r >= (unsigned)MT_RING) r -= MT_RING;
+        return r;
+    };
     const int bounds[4] = {0, MT_N - MT_M, 2 * (MT_N - MT_M), MT_N};
     for (int ph = 0; ph < 3; ph++) {
-        for (int i = bounds[ph] + lane; i < bounds[ph + 1]; i += nlanes) {
-            const unsigned long long r = g + i;
-            s->x[r % MT_RING] = mt_twist(s->x[(r - MT_N) % MT_RING], s->x[(r - MT_N + 1) % MT_RING],
-                                         s->x[(r - MT_N + MT_M) % MT_RING]);
-        }
+        for (int i = bounds[ph] + lane; i < bounds[ph + 1]; i += nlanes)
+            s->x[slot(i)] = mt_twist(s->x[slot(i - MT_N)], s->x[slot(i - MT_N + 1)], s->x[slot(i - MT_N + MT_M)]);
         sync();
     }
     if (lane == 0) s->gen = g + MT_N;
