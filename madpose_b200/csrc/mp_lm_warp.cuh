@@ -30,6 +30,40 @@ __device__ __forceinline__ void warp_compress(const LmSetup &L, const double *to
     __syncwarp();
 }
 
+// lm_plus, one ambient component per lane: returns component `lane` (< LM_NA) of Plus(x, sign * dsrc) projected onto
+// the bounds; dsrc is the compact tangent vector (shared memory).  Same expressions per component as lm_plus.
+__device__ __forceinline__ double warp_plus_component(const LmSetup &L, const double *x, const double *dsrc, double sign, int lane) {
+    const int k = lane < LM_NA ? lane : 0;
+    auto dv = [&](int s_) { const int c = L.slot[s_]; return c >= 0 ? sign * dsrc[c] : 0.0; };
+    double v;
+    if (k == 0 || k >= 5) v = x[k] + dv(k == 0 ? 0 : k - 1);
+    else {
+        const double d1 = dv(1), d2 = dv(2), d3 = dv(3);
+        const double n = sqrt(d1 * d1 + d2 * d2 + d3 * d3);
+        v = x[k];
+        if (n > 0) {
+            double sv, e0;
+            sincos(n, &sv, &e0);
+            const double sn = sv / n, e1 = sn * d1, e2 = sn * d2, e3 = sn * d3;
+            const double *q = x + 1;
+            if (k == 1) v = e0 * q[0] - e1 * q[1] - e2 * q[2] - e3 * q[3];
+            else if (k == 2) v = e0 * q[1] + e1 * q[0] + e2 * q[3] - e3 * q[2];
+            else if (k == 3) v = e0 * q[2] - e1 * q[3] + e2 * q[0] + e3 * q[1];
+            else v = e0 * q[3] + e1 * q[2] - e2 * q[1] + e3 * q[0];
+        }
+    }
+    if (L.has_lower[k] && v < L.lower[k]) v = L.lower[k];
+    return v;
+}
+// LmDriver::grad_max on the warp: max_k |Plus(x, -g)_k - x_k|, valid on every lane
+__device__ __forceinline__ double warp_grad_max(const LmSetup &L, const double *x, const double *g, int lane) {
+    const double v = warp_plus_component(L, x, g, -1.0, lane);
+    double m = lane < LM_NA ? fabs(v - x[lane < LM_NA ? lane : 0]) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(LMW_FULL, m, o));
+    return m;
+}
+
 // LmDriver::first
 #define LMW_T0() long long lmw_t_ = clock64()
 #define LMW_T(slot_) do { if (lane == 0) { const long long n_ = clock64(); d.prof[slot_] += (unsigned long long)(n_ - lmw_t_); lmw_t_ = n_; } } while (0)
@@ -41,11 +75,12 @@ __device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     if (lane < nt) d.scale[lane] = 1.0 / (1.0 + sqrt(d.A[lane * nt + lane]));
     __syncwarp();
     int go = 0;
+    const double gm0 = warp_grad_max(L, d.x, d.g, lane);
     if (lane == 0) {
         d.cost = tot[LM_TRI + LM_NT];
         d.info.cost0 = d.cost; d.info.cost = d.cost;
         if (!finite_d(d.cost)) d.info.termination = 3;
-        else if (d.grad_max(d.x, d.g) <= L.gtol) d.info.termination = 1;
+        else if (gm0 <= L.gtol) d.info.termination = 1;
         else {
             d.radius = 1e4; d.decrease = 2.0;
             d.min_cost = d.cur_cost = d.ref_cost = d.cand_cost = d.cost; d.acc_ref = 0; d.acc_cand = 0;
@@ -196,17 +231,17 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
             __syncwarp();
             continue;
         }
-        if (lane == 0) {
-            d.mcc = mcc;
-            d.n_invalid = 0;
-            double dd[LM_NT];
+        if (lane == 0) { d.mcc = mcc; d.n_invalid = 0; }
+        if (rowl) { // the step in the unscaled tangent space, one entry per lane
+            double mine = 0.0;
 #pragma unroll
-            for (int a = 0; a < LM_NT; a++) {
-                dd[a] = LMW_IN(a) ? xs[a] * d.scale[a] : 0.0;
-                if (LMW_IN(a)) d.y[a] = xs[a];
-            }
-            lm_plus(L, d.x, dd, d.xc);
+            for (int a = 0; a < LM_NT; a++)
+                if (a == lane) mine = xs[a];
+            d.y[lane] = mine * d.scale[lane];
         }
+        __syncwarp();
+        const double xcv = warp_plus_component(L, d.x, d.y, 1.0, lane);
+        if (lane < LM_NA) d.xc[lane] = xcv;
         __syncwarp();
         LMW_T(6);
         return true;
@@ -227,11 +262,13 @@ __device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
     warp_compress(L, tot, d.An, d.gn, lane);
     int verdict = 0; // 0 finished, 1 rejected step (continue), 2 accepted step
     double cc = 0, rel = 0;
+    double sn = 0, xn = 0; // |xc - x|^2 and |x|^2: one component per lane, butterfly sums
+    if (lane < LM_NA) { const double xv = d.x[lane], dx = d.xc[lane] - xv; sn = dx * dx; xn = xv * xv; }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) { sn += __shfl_xor_sync(LMW_FULL, sn, o); xn += __shfl_xor_sync(LMW_FULL, xn, o); }
     if (lane == 0) {
         cc = tot[LM_TRI + LM_NT];
         if (!finite_d(cc)) cc = DBL_MAX;
-        double sn = 0, xn = 0;
-        for (int k = 0; k < LM_NA; k++) { sn += (d.xc[k] - d.x[k]) * (d.xc[k] - d.x[k]); xn += d.x[k] * d.x[k]; }
         if (sqrt(sn) <= L.ptol * (sqrt(xn) + L.ptol)) { d.info.termination = 1; d.info.cost = d.cost; }
         else if (fabs(d.cost - cc) <= L.ftol * d.cost) { d.info.termination = 1; d.info.cost = d.cost; }
         else {
@@ -245,8 +282,10 @@ __device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
         for (int e = lane; e < nt * nt; e += 32) d.A[e] = d.An[e];
         if (lane < nt) d.g[lane] = d.gn[lane];
         __syncwarp();
+        if (lane < LM_NA) d.x[lane] = d.xc[lane];
+        __syncwarp();
+        const double gm = warp_grad_max(L, d.x, d.g, lane);
         if (lane == 0) {
-            for (int k = 0; k < LM_NA; k++) d.x[k] = d.xc[k];
             d.cost = cc;
             const double tt = 2.0 * rel - 1.0;
             d.radius = fmin(1e16, d.radius / fmax(1.0 / 3.0, 1.0 - tt * tt * tt));
@@ -255,7 +294,7 @@ __device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
             if (d.cur_cost < d.min_cost) { d.min_cost = d.cur_cost; d.n_nonmono = 0; d.cand_cost = d.cur_cost; d.acc_cand = 0; }
             else { ++d.n_nonmono; if (d.cur_cost > d.cand_cost) { d.cand_cost = d.cur_cost; d.acc_cand = 0; } }
             if (d.n_nonmono == L.max_nonmono) { d.ref_cost = d.cand_cost; d.acc_ref = d.acc_cand; }
-            if (d.grad_max(d.x, d.g) <= L.gtol) { d.info.termination = 1; d.info.cost = d.cost; verdict = 0; }
+            if (gm <= L.gtol) { d.info.termination = 1; d.info.cost = d.cost; verdict = 0; }
         }
         verdict = __shfl_sync(LMW_FULL, verdict, 0);
     }
