@@ -217,7 +217,7 @@ def main():
             "rounds_per_step": rounds / a.steps,
             "kernel_ms_per_step_single_stream": share, "single_stream_ms_per_step": single_stream_ms,
             "decide_phase_gcycles": {k2: round(v / 1e9, 3) for k2, v in phase_cycles.items()},
-            "roofline": {"bound": bound, "kernel": dom, "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "roofline": {"bound": bound, "kernel": {"decide": "scan_kernel + lo_kernel (fp64 re-score, inliers, local optimisation / LM)"}.get(dom, dom), "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach / peak, "traffic": None,
                          "peak_source": "register-only FFMA / DFMA probes measured in this run (fp32 %.1f, fp64 %.1f TFLOP/s); "
                                         "MEASURED_PEAKS.json holds HBM and bf16 tensor peaks only" % (peak32, peak64),
