@@ -98,11 +98,11 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     const int gsz = (n_pairs + G - 1) / G;
     G = (n_pairs + gsz - 1) / gsz;
     constexpr int SLOTS = 4, NSIDE = 12;
-    MP_CUDA(A.misc.reserve(128 + 16 * MP_MAX_GROUPS));
+    MP_CUDA(A.misc.reserve(128 + 24 * MP_MAX_GROUPS));
     MP_CUDA(A.items.reserve(2 * (size_t)n_pairs * LP_BMAX * sizeof(int)));
-    MP_CUDA(A.h_active.reserve(4 * (2 + SLOTS) * MP_MAX_GROUPS));
+    MP_CUDA(A.h_active.reserve(4 * (2 + 2 * SLOTS) * MP_MAX_GROUPS));
     MP_CUDA(A.lo_req.reserve(n_pairs * sizeof(int)));
-    int *h_active = A.h_active.as<int>(), *h_iter = h_active + G, *h_side = h_active + 2 * G; // h_side[g * SLOTS + k]
+    int *h_active = A.h_active.as<int>(), *h_iter = h_active + G, *h_side = h_active + 2 * G; // h_side[2 * (g * SLOTS + k)] = {pairs not done, pairs handed back so far}
     for (int g = 0; g < G; g++) { h_active[g] = std::min(gsz, n_pairs - g * gsz); h_iter[g] = 0; }
     while ((int)c->gstream.size() < G) {
         cudaStream_t gs; cudaEvent_t ge;
@@ -133,6 +133,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.n_active = reinterpret_cast<int *>(A.misc.as<char>() + 128);
     L.n_iter = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 4 * MP_MAX_GROUPS);
     L.n_items = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 8 * MP_MAX_GROUPS);
+    L.n_ret = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 16 * MP_MAX_GROUPS);
+    MP_CUDA(cudaMemsetAsync(L.n_ret, 0, G * sizeof(int), s));
     L.items = A.items.as<int>(); L.n_pairs = n_pairs;
     L.lo_req = A.lo_req.as<int>();
     L.gsz = gsz;
@@ -164,6 +166,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaEventRecord(c->ev_init, s));
     struct GroupRt {
         int act = 0, iter = 1;        // latest known: pairs not done; pairs left iterating by the last scan
+        int ret_seen = 0;             // pairs handed back to PH_ITER by lo_kernel launches, as last seen
         bool main_pending = false, lo_returned = true;
         bool slot_busy[SLOTS] = {false, false, false, false};
         long long round = 0;
@@ -207,7 +210,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, ss));
         else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, ss));
         if (serial) MP_CUDA(tick(-1));
-        MP_CUDA(cudaMemcpyAsync(h_side + g * SLOTS + slot, L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
+        MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot), L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
+        MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot) + 1, L.n_ret + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaEventRecord(c->sev[g * SLOTS + slot], ss));
         launches += 5;
         return MP_OK;
@@ -226,8 +230,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
                 if (q == cudaErrorNotReady) { side_busy = true; continue; }
                 MP_CUDA(q);
                 R.slot_busy[k] = false;
-                R.act = std::min(R.act, h_side[g * SLOTS + k]);
-                R.lo_returned = true;
+                R.act = std::min(R.act, h_side[2 * (g * SLOTS + k)]);
+                if (h_side[2 * (g * SLOTS + k) + 1] > R.ret_seen) { R.ret_seen = h_side[2 * (g * SLOTS + k) + 1]; R.lo_returned = true; }
                 if (trace) fprintf(stderr, "[mp] %8.2f ms  g%d  lo slot %d done   act %d\n", now_ms(), g, k, R.act);
                 progress = true;
             }

@@ -290,6 +290,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
         *reinterpret_cast<volatile int *>(L.lo_req + p) = 0;
         __threadfence();
         atomicExch(&L.st[p].phase, final_phase);
+        if (final_phase == PH_ITER) atomicAdd(L.n_ret + p / L.gsz, 1);
         if (final_phase == PH_DONE) {
             atomicSub(L.n_active + p / L.gsz, 1);
             for (int q = 0; q < 16; q++) atomicAdd(L.clk + q, S.clk[q]);
