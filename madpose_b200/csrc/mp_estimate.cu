@@ -98,7 +98,9 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     const int gsz = (n_pairs + G - 1) / G;
     G = (n_pairs + gsz - 1) / gsz;
     constexpr int SLOTS = 4, NSIDE = 12;
-    MP_CUDA(A.misc.reserve(128 + 24 * MP_MAX_GROUPS));
+    MP_CUDA(A.misc.reserve(128 + 28 * MP_MAX_GROUPS));
+    MP_CUDA(A.cand.reserve(slots * sizeof(int)));
+    MP_CUDA(A.cand_ok.reserve(slots));
     MP_CUDA(A.items.reserve(2 * (size_t)n_pairs * LP_BMAX * sizeof(int)));
     MP_CUDA(A.h_active.reserve(4 * (2 + 2 * SLOTS) * MP_MAX_GROUPS));
     MP_CUDA(A.lo_req.reserve(n_pairs * sizeof(int)));
@@ -134,6 +136,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.n_iter = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 4 * MP_MAX_GROUPS);
     L.n_items = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 8 * MP_MAX_GROUPS);
     L.n_ret = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 16 * MP_MAX_GROUPS);
+    L.n_cand = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 24 * MP_MAX_GROUPS);
+    L.cand = A.cand.as<int>(); L.cand_ok = A.cand_ok.as<unsigned char>();
     MP_CUDA(cudaMemsetAsync(L.n_ret, 0, G * sizeof(int), s));
     L.items = A.items.as<int>(); L.n_pairs = n_pairs;
     L.lo_req = A.lo_req.as<int>();
@@ -187,6 +191,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         const int round = (int)(++gr[g].round);
         MP_CUDA(cudaMemsetAsync(L.n_iter + g, 0, sizeof(int), gs));
         MP_CUDA(cudaMemsetAsync(L.n_items + 2 * g, 0, 2 * sizeof(int), gs));
+        MP_CUDA(cudaMemsetAsync(L.n_cand + g, 0, sizeof(int), gs));
         if (serial) MP_CUDA(tick(0));
         sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
         if (serial) MP_CUDA(tick(1));
@@ -213,7 +218,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot), L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot) + 1, L.n_ret + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaEventRecord(c->sev[g * SLOTS + slot], ss));
-        launches += 5;
+        launches += 7;
         return MP_OK;
     };
     const bool trace = getenv("MP_TRACE") != nullptr; // host-side timeline of the rounds on stderr (debugging aid)

@@ -79,6 +79,9 @@ struct LoopBuffers {
     int *sample;    // [3 * off + pad] scratch: un-flattened sample lists
     int *n_active;  // device counters of pairs not yet PH_DONE, one per group of gsz consecutive pairs
     int *n_iter;    // per group: pairs left in PH_ITER by the last scan kernel
+    int *n_cand;    // per group: point-solver candidates of this round (reset every round)
+    int *cand;      // [n_pairs * LP_BMAX * LP_MM] candidate list of the round: item * LP_MM + j (a group uses its own slice)
+    unsigned char *cand_ok; // per model slot: did the candidate survive its tail
     int *n_ret;     // per group: pairs handed back to PH_ITER by lo_kernel launches so far (cumulative)
     int *n_items;   // per group: [2] number of samples of this round per minimal solver (reset every round)
     int *items;     // [2][n_pairs * LP_BMAX] samples of this round, (pair - first) * LP_BMAX + b, grouped per solver so that

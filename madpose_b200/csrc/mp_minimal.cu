@@ -10,8 +10,13 @@
 namespace mp {
 
 __device__ __noinline__ int minimal_solver_ni(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx,
-                                              bool min_depth_on, Model *out) {
-    return minimal_solver(pc, M, solver_idx, idx, min_depth_on, out);
+                                              bool min_depth_on, Model *out, bool with_tail = true) {
+    return minimal_solver(pc, M, solver_idx, idx, min_depth_on, out, with_tail);
+}
+__device__ __noinline__ bool minimal_tail_ni(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on, Model *m) {
+    if (pc.kind == CALIB) return minimal_points_tail<CALIB>(pc, M, idx, min_depth_on, m);
+    if (pc.kind == SHARED) return minimal_points_tail<SHARED>(pc, M, idx, min_depth_on, m);
+    return minimal_points_tail<TWO>(pc, M, idx, min_depth_on, m);
 }
 
 // K1/K2 stand-alone: one thread per sample of one pair (mp_minimal_solve_batch)
@@ -43,16 +48,73 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
     PairWork &W = L.wk[p];
     const PairConst &pc = L.pc[p];
     Model tmp[LP_MM];
-    const int c = minimal_solver_ni(pc, L.M + pc.off, W.solver[b], W.idx[b], prm.cfg.min_depth_constraint != 0, tmp);
+    const int solver = W.solver[b];
+    // point-only solver: candidates only; their tail (triangulation, depth fits) runs in minimal_tail_kernel with one
+    // thread per candidate, so that it does not serialise over lanes holding different numbers of candidates
+    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], prm.cfg.min_depth_constraint != 0, tmp, solver == 0);
     W.count[b] = c;
     Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
     HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
-    for (int j = 0; j < c; j++) { out[j] = tmp[j]; pack_hyp(pc.kind, tmp[j], hy + j); }
+    if (solver == 0) {
+        for (int j = 0; j < c; j++) { out[j] = tmp[j]; pack_hyp(pc.kind, tmp[j], hy + j); }
+    } else {
+        for (int j = 0; j < c; j++) out[j] = tmp[j];
+        if (c > 0) {
+            const int base = atomicAdd(L.n_cand + grp, c);
+            int *cl = L.cand + (size_t)first * LP_BMAX * LP_MM;
+            for (int j = 0; j < c; j++) cl[base + j] = item * LP_MM + j;
+        }
+    }
 }
 
+// tail of the point-only solvers, one thread per candidate of the round (dense: the list was filled with atomics)
+__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_tail_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    const LoopParams &prm = *prmp;
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int grp = first / L.gsz;
+    if (g >= L.n_cand[grp]) return;
+    const int e = L.cand[(size_t)first * LP_BMAX * LP_MM + g];
+    const int item = e / LP_MM, j = e % LP_MM;
+    const int p = first + item / LP_BMAX, b = item % LP_BMAX;
+    const PairConst &pc = L.pc[p];
+    const PairWork &W = L.wk[p];
+    Model *slot = L.models + ((size_t)p * LP_BMAX + b) * LP_MM + j;
+    Model m = *slot;
+    const bool ok = minimal_tail_ni(pc, L.M + pc.off, W.idx[b], prm.cfg.min_depth_constraint != 0, &m);
+    if (ok) *slot = m;
+    L.cand_ok[((size_t)p * LP_BMAX + b) * LP_MM + j] = ok ? 1 : 0;
+}
+
+// compaction of the surviving candidates of every point-solver sample, in order, + fp32 packs
+__global__ void __launch_bounds__(64) minimal_pack_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    const int grp = first / L.gsz;
+    if (g >= L.n_items[2 * grp + 1]) return;
+    const int item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + g];
+    const int p = first + item / LP_BMAX, b = item % LP_BMAX;
+    const PairConst &pc = L.pc[p];
+    PairWork &W = L.wk[p];
+    Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
+    HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
+    const unsigned char *ok = L.cand_ok + ((size_t)p * LP_BMAX + b) * LP_MM;
+    const int c = W.count[b];
+    int k = 0;
+    for (int j = 0; j < c; j++) {
+        if (!ok[j]) continue;
+        const Model m = out[j];
+        if (k != j) out[k] = m;
+        pack_hyp(pc.kind, m, hy + k);
+        k++;
+    }
+    W.count[b] = k;
+}
 
 cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, cudaStream_t s) {
     minimal_batch_kernel<<<(count * LP_BMAX + 32 + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
+    // worst case of the candidate list: every sample of the round is a point-solver sample with LP_MM candidates; the
+    // threads beyond the actual count exit at once
+    minimal_tail_kernel<<<(count * LP_BMAX * LP_MM + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
+    minimal_pack_kernel<<<(count * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
     return cudaGetLastError();
 }
 

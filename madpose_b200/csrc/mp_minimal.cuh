@@ -95,10 +95,10 @@ template <int NPT> MP_HD bool depth_fit_tail(const PairConst &pc, const double *
     return model_finite(*m);
 }
 
-template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on,
-                                             Model *out) {
-    constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
-    double b0[NPT][3], b1[NPT][3], p0[NPT][2], p1[NPT][2], d0[NPT], d1[NPT];
+// the sample of the point-only solvers: unit bearings b0/b1, homogeneous image points p0/p1 (K^-1-normalised when
+// calibrated), prior depths
+template <int KIND, int NPT> MP_HD void load_point_sample(const PairConst &pc, const Match64 *M, const int *idx, double (*b0)[3],
+                                                         double (*b1)[3], double (*p0)[2], double (*p1)[2], double *d0, double *d1) {
     for (int k = 0; k < NPT; k++) {
         const Match64 m = M[idx[k]];
         double a[3], b[3];
@@ -109,6 +109,15 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
         p0[k][0] = a[0]; p0[k][1] = a[1]; p1[k][0] = b[0]; p1[k][1] = b[1];
         d0[k] = m.d0; d1[k] = m.d1;
     }
+}
+
+// with_tail = false: the candidates (R, t, f0, f1) are returned WITHOUT the triangulation / depth-fit tail; the device
+// loop runs that tail in minimal_tail_kernel, one thread per candidate (mp_minimal.cu)
+template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on,
+                                             Model *out, bool with_tail = true) {
+    constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
+    double b0[NPT][3], b1[NPT][3], p0[NPT][2], p1[NPT][2], d0[NPT], d1[NPT];
+    load_point_sample<KIND, NPT>(pc, M, idx, b0, b1, p0, p1, d0, d1);
     int n = 0;
     if (KIND == CALIB) {
         Pose poses[10];
@@ -118,6 +127,7 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
             for (int k = 0; k < 9; k++) m.R[k] = poses[q].R[k];
             for (int k = 0; k < 3; k++) m.t[k] = poses[q].t[k];
             m.f0 = 1.0; m.f1 = 1.0;
+            if (!with_tail) { m.scale = 1; m.o0 = 0; m.o1 = 0; out[n++] = m; continue; }
             if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, 1.0, 1.0, min_depth_on, &m)) out[n++] = m;
         }
     } else if (KIND == SHARED) {
@@ -130,6 +140,7 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
             for (int k = 0; k < 9; k++) m.R[k] = fps[q].pose.R[k];
             for (int k = 0; k < 3; k++) m.t[k] = fps[q].pose.t[k];
             m.f0 = fps[q].focal; m.f1 = fps[q].focal;
+            if (!with_tail) { m.scale = 1; m.o0 = 0; m.o1 = 0; out[n++] = m; continue; }
             if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, m.f0, m.f1, min_depth_on, &m)) out[n++] = m;
         }
     } else {
@@ -146,23 +157,33 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
             Model m;
             recover_pose<NPT>(E, p0, p1, 1e9, m.R, m.t); // un-calibrated points with K = I, as the reference does
             m.f0 = f0; m.f1 = f1;
+            if (!with_tail) { m.scale = 1; m.o0 = 0; m.o1 = 0; out[n++] = m; continue; }
             if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, f0, f1, min_depth_on, &m)) out[n++] = m;
         }
     }
     return n;
 }
 
+// the tail of minimal_points on ONE candidate (R, t, f0, f1 set): triangulation + affine depth fits
+template <int KIND> MP_HD bool minimal_points_tail(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on,
+                                                   Model *m) {
+    constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
+    double b0[NPT][3], b1[NPT][3], p0[NPT][2], p1[NPT][2], d0[NPT], d1[NPT];
+    load_point_sample<KIND, NPT>(pc, M, idx, b0, b1, p0, p1, d0, d1);
+    return depth_fit_tail<NPT>(pc, d0, d1, p0, p1, m->f0, m->f1, min_depth_on, m);
+}
+
 // dispatch; out must hold kMaxModelsAny models
 MP_HD int minimal_solver(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx, bool min_depth_on,
-                         Model *out) {
+                         Model *out, bool with_tail = true) {
     if (solver_idx == 0) {
         if (pc.kind == CALIB) return minimal_affine<CALIB>(pc, M, idx, min_depth_on, out);
         if (pc.kind == SHARED) return minimal_affine<SHARED>(pc, M, idx, min_depth_on, out);
         return minimal_affine<TWO>(pc, M, idx, min_depth_on, out);
     }
-    if (pc.kind == CALIB) return minimal_points<CALIB>(pc, M, idx, min_depth_on, out);
-    if (pc.kind == SHARED) return minimal_points<SHARED>(pc, M, idx, min_depth_on, out);
-    return minimal_points<TWO>(pc, M, idx, min_depth_on, out);
+    if (pc.kind == CALIB) return minimal_points<CALIB>(pc, M, idx, min_depth_on, out, with_tail);
+    if (pc.kind == SHARED) return minimal_points<SHARED>(pc, M, idx, min_depth_on, out, with_tail);
+    return minimal_points<TWO>(pc, M, idx, min_depth_on, out, with_tail);
 }
 
 } // namespace mp
