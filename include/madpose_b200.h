@@ -141,6 +141,13 @@ int mp_last_timing(mp_ctx *ctx, double *kernel_ms, double *total_ms, int *launch
  * scores_f32: fused fp32 scoring kernel; scores_f64: exact fp64 evaluation. Either may be NULL. */
 int mp_score_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
                    int n_models, const mp_model *models, float *scores_f32, double *scores_f64);
+/* The step before the path: madpose.utils.get_depths (madpose/utils.py:4-22) -- nearest-neighbour
+ * lookup of the prior depth of n keypoints in a depth map of another resolution: scale the keypoints by
+ * (map_w / img_w, map_h / img_h), round half to even (numpy.round), clip to the map, gather.
+ * depth_map: HOST buffer, row-major map_h x map_w, elem_size 4 (float) or 8 (double); mkpts: n x 2 doubles (x, y);
+ * out: n doubles.  Keeps the gather on the device for callers whose depth maps come from a network. */
+int mp_get_depths(mp_ctx *ctx, const void *depth_map, int elem_size, int map_h, int map_w, int img_h, int img_w,
+                  const double *mkpts, int n, double *out);
 /* GetInliers (hybrid_ransac.h:289-349): ascending indices with r^2 < thr[t] (thr in
  * the front-end's rescaled units, 3 entries); out_idx has 3*n entries (type t at t*n). */
 int mp_inliers(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,

@@ -123,7 +123,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
-    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch",
+    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths",
 ]
 
 
@@ -188,6 +188,18 @@ class Context:
             self.ctx, kind, C.byref(pair), C.byref(opt), C.byref(cfg), nm, m.ctypes.data_as(C.c_void_p),
             s32.ctypes.data_as(C.c_void_p) if want32 else None, s64.ctypes.data_as(C.c_void_p) if want64 else None))
         return s32, s64
+
+    def get_depths(self, image_shape, depth_map, mkpts):
+        """madpose.utils.get_depths(image, depth_map, mkpts) with the image given by its shape (H, W[, C])."""
+        dm = np.ascontiguousarray(depth_map)
+        if dm.dtype not in (np.float32, np.float64):
+            dm = dm.astype(np.float64)
+        kp = np.ascontiguousarray(mkpts, np.float64).reshape(-1, 2)
+        out = np.empty(kp.shape[0], np.float64)
+        self._check(self.lib.mp_get_depths(self.ctx, dm.ctypes.data_as(C.c_void_p), dm.dtype.itemsize, dm.shape[0], dm.shape[1],
+                                           int(image_shape[0]), int(image_shape[1]), kp.ctypes.data_as(C.c_void_p),
+                                           kp.shape[0], out.ctypes.data_as(C.c_void_p)))
+        return out.astype(dm.dtype)
 
     def inliers(self, kind, pair, opt, cfg, model, thr3):
         m = np.ascontiguousarray(model, np.float64).reshape(MODEL_DOUBLES)

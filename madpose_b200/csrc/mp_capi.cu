@@ -88,6 +88,19 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
     return MP_OK;
 }
 
+// madpose.utils.get_depths (madpose/utils.py:4-22) on the device: one thread per keypoint
+template <class T>
+__global__ void get_depths_kernel(const T *map, int map_h, int map_w, double rx, double ry, const double2 *kp, int n, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double2 p = kp[i];
+    // numpy.round = round half to even = rint; astype(int) of an integral double; then numpy.clip
+    double cx = rint(p.x * rx), cy = rint(p.y * ry);
+    cx = fmin(fmax(cx, 0.0), (double)(map_w - 1));
+    cy = fmin(fmax(cy, 0.0), (double)(map_h - 1));
+    out[i] = (double)map[(size_t)(long long)cy * map_w + (long long)cx];
+}
+
 } // namespace mp
 using namespace mp;
 
@@ -170,6 +183,37 @@ int mp_last_timing(mp_ctx *c, double *kernel_ms, double *total_ms, int *launches
     if (kernel_ms) *kernel_ms = c->last_kernel_ms;
     if (total_ms) *total_ms = c->last_total_ms;
     if (launches) *launches = c->last_launches;
+    return MP_OK;
+}
+
+int mp_get_depths(mp_ctx *c, const void *depth_map, int elem_size, int map_h, int map_w, int img_h, int img_w,
+                  const double *mkpts, int n, double *out) {
+    if (!c || !depth_map || !mkpts || !out || n <= 0 || map_h <= 0 || map_w <= 0 || img_h <= 0 || img_w <= 0)
+        return fail(MP_ERR_ARG, "mp_get_depths: bad arguments");
+    if (elem_size != 4 && elem_size != 8) return fail(MP_ERR_ARG, "mp_get_depths: elem_size must be 4 (float) or 8 (double)");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    const size_t map_bytes = (size_t)map_h * map_w * elem_size;
+    MP_CUDA(c->d_work.reserve(map_bytes));
+    MP_CUDA(c->d_idx.reserve((size_t)n * 2 * sizeof(double)));
+    MP_CUDA(c->d_scores64.reserve((size_t)n * sizeof(double)));
+    MP_CUDA(cudaMemcpyAsync(c->d_work.p, depth_map, map_bytes, cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(c->d_idx.p, mkpts, (size_t)n * 2 * sizeof(double), cudaMemcpyHostToDevice, s));
+    const double rx = (double)map_w / (double)img_w, ry = (double)map_h / (double)img_h; // utils.py:6-11
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    if (elem_size == 4)
+        get_depths_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(c->d_work.as<float>(), map_h, map_w, rx, ry, c->d_idx.as<double2>(), n,
+                                                              c->d_scores64.as<double>());
+    else
+        get_depths_kernel<double><<<(n + 255) / 256, 256, 0, s>>>(c->d_work.as<double>(), map_h, map_w, rx, ry, c->d_idx.as<double2>(), n,
+                                                               c->d_scores64.as<double>());
+    MP_CUDA(cudaGetLastError());
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    MP_CUDA(cudaMemcpyAsync(out, c->d_scores64.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float ms = 0;
+    MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 1;
     return MP_OK;
 }
 
