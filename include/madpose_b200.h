@@ -148,6 +148,12 @@ int mp_score_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options 
  * out: n doubles.  Keeps the gather on the device for callers whose depth maps come from a network. */
 int mp_get_depths(mp_ctx *ctx, const void *depth_map, int elem_size, int map_h, int map_w, int img_h, int img_w,
                   const double *mkpts, int n, double *out);
+/* The step after the path: madpose.utils.compute_pose_error (madpose/utils.py:59-78, with
+ * angle_error_vec :52-56 and angle_error_mat :46-49) for n estimated poses against n ground truths.
+ * T_0to1: n x 16 (row-major 4x4), R: n x 9 (row-major), t: n x 3; t_thres < 0 means None (utils.py:66).
+ * err_t / err_R: n doubles each, in degrees (err_t folded to [0, 90]: the sign ambiguity of E). */
+int mp_pose_errors(mp_ctx *ctx, int n, const double *T_0to1, const double *R, const double *t, double t_thres,
+                   double *err_t, double *err_R);
 /* GetInliers (hybrid_ransac.h:289-349): ascending indices with r^2 < thr[t] (thr in
  * the front-end's rescaled units, 3 entries); out_idx has 3*n entries (type t at t*n). */
 int mp_inliers(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,

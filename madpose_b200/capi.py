@@ -123,7 +123,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
-    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths",
+    "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
 ]
 
 
@@ -200,6 +200,20 @@ class Context:
                                            int(image_shape[0]), int(image_shape[1]), kp.ctypes.data_as(C.c_void_p),
                                            kp.shape[0], out.ctypes.data_as(C.c_void_p)))
         return out.astype(dm.dtype)
+
+    def pose_errors(self, T_0to1, R, t, t_thres=None):
+        """madpose.utils.compute_pose_error for n poses: T_0to1 (n,4,4), R (n,3,3), t (n,3) -> (err_t, err_R) in degrees."""
+        T = np.ascontiguousarray(T_0to1, np.float64).reshape(-1, 16)
+        Rm = np.ascontiguousarray(R, np.float64).reshape(-1, 9)
+        tv = np.ascontiguousarray(t, np.float64).reshape(-1, 3)
+        n = T.shape[0]
+        if Rm.shape[0] != n or tv.shape[0] != n:
+            raise ValueError("pose_errors: T_0to1, R and t must describe the same number of poses")
+        et, er = np.empty(n, np.float64), np.empty(n, np.float64)
+        self._check(self.lib.mp_pose_errors(self.ctx, n, T.ctypes.data_as(C.c_void_p), Rm.ctypes.data_as(C.c_void_p),
+                                            tv.ctypes.data_as(C.c_void_p), C.c_double(-1.0 if t_thres is None else t_thres),
+                                            et.ctypes.data_as(C.c_void_p), er.ctypes.data_as(C.c_void_p)))
+        return et, er
 
     def inliers(self, kind, pair, opt, cfg, model, thr3):
         m = np.ascontiguousarray(model, np.float64).reshape(MODEL_DOUBLES)

@@ -101,6 +101,30 @@ __global__ void get_depths_kernel(const T *map, int map_h, int map_w, double rx,
     out[i] = (double)map[(size_t)(long long)cy * map_w + (long long)cx];
 }
 
+// madpose.utils.compute_pose_error (madpose/utils.py:46-78): one thread per pose
+__global__ void pose_errors_kernel(int n, const double *Tgt, const double *R, const double *t, double t_thres, double *err_t,
+                                   double *err_R) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double *T = Tgt + 16 * (size_t)i, *Ri = R + 9 * (size_t)i, *ti = t + 3 * (size_t)i;
+    const double RAD2DEG = 57.29577951308232;
+    double tg[3] = {T[3], T[7], T[11]};
+    double dot = 0, n1 = 0, n2 = 0, tr = 0;
+    for (int k = 0; k < 3; ++k) {
+        dot += ti[k] * tg[k]; n1 += ti[k] * ti[k]; n2 += tg[k] * tg[k];
+        for (int j = 0; j < 3; ++j) tr += Ri[3 * k + j] * T[4 * k + j]; // trace(R^T R_gt)
+    }
+    double c = dot / (sqrt(n1) * sqrt(n2));
+    c = c < -1.0 ? -1.0 : (c > 1.0 ? 1.0 : c); // numpy.clip keeps a NaN (zero-length translation)
+    double et = RAD2DEG * acos(c);
+    et = (et != et || 180.0 - et != 180.0 - et) ? et : fmin(et, 180.0 - et); // numpy.minimum propagates NaN
+    double cr = (tr - 1.0) * 0.5;
+    cr = cr < -1.0 ? -1.0 : (cr > 1.0 ? 1.0 : cr);
+    if (t_thres >= 0.0 && sqrt(n2) < t_thres) et = 0.0;
+    err_t[i] = et;
+    err_R[i] = RAD2DEG * fabs(acos(cr));
+}
+
 } // namespace mp
 using namespace mp;
 
@@ -210,6 +234,31 @@ int mp_get_depths(mp_ctx *c, const void *depth_map, int elem_size, int map_h, in
     MP_CUDA(cudaGetLastError());
     MP_CUDA(cudaEventRecord(c->ev[1], s));
     MP_CUDA(cudaMemcpyAsync(out, c->d_scores64.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float ms = 0;
+    MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 1;
+    return MP_OK;
+}
+
+int mp_pose_errors(mp_ctx *c, int n, const double *T_0to1, const double *R, const double *t, double t_thres, double *err_t,
+                   double *err_R) {
+    if (!c || n <= 0 || !T_0to1 || !R || !t || !err_t || !err_R) return fail(MP_ERR_ARG, "mp_pose_errors: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    MP_CUDA(c->d_work.reserve((size_t)n * 28 * sizeof(double)));
+    MP_CUDA(c->d_scores64.reserve((size_t)n * 2 * sizeof(double)));
+    double *dT = c->d_work.as<double>(), *dR = dT + 16 * (size_t)n, *dt = dR + 9 * (size_t)n;
+    double *dout = c->d_scores64.as<double>();
+    MP_CUDA(cudaMemcpyAsync(dT, T_0to1, (size_t)n * 16 * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dR, R, (size_t)n * 9 * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dt, t, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    pose_errors_kernel<<<(n + 127) / 128, 128, 0, s>>>(n, dT, dR, dt, t_thres, dout, dout + n);
+    MP_CUDA(cudaGetLastError());
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    MP_CUDA(cudaMemcpyAsync(err_t, dout, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(err_R, dout + n, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaStreamSynchronize(s));
     float ms = 0;
     MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
