@@ -127,7 +127,8 @@ int mp_last_breakdown(mp_ctx *ctx, double *class_ms4, int *class_launches4, int 
  * 0 = automatic (about 750 pairs per group, at most 8 groups); 1 = everything on one stream (the per-class kernel
  * timings of mp_last_breakdown are exact only then). */
 int mp_set_groups(mp_ctx *ctx, int groups);
-/* RANSAC iterations speculated per pair per round (1..64; 0 = default 64).  Results do not depend on it. */
+/* Upper bound of the RANSAC iterations speculated per pair per round (1..256; 0 = default 128).  A pair starts with 64
+ * and doubles its batch after every round that found no new best model.  Results do not depend on it. */
 int mp_set_batch(mp_ctx *ctx, int iterations);
 /* profiling aid: SM-clock cycles (one thread per pair's CTA, summed over pairs) the decide kernel spent in
  * {sequential scan, GetInliers, fp64 ScoreModel, LM evaluation, LM solves total, shuffles, un-flatten, LO total} */

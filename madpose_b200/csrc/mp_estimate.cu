@@ -83,11 +83,11 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.h_active.reserve(4 * MP_MAX_GROUPS));
     LoopParams *prm = A.h_prm.as<LoopParams>();
-    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BMAX;
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BDEF;
     {
         const char *e = getenv("MP_B_AFTER_LO"); // experiments
         const int v = e ? atoi(e) : 0;
-        prm->b_after_lo = v > 0 ? std::min(v, prm->bmax) : prm->bmax; // measured on configs[1]: 16 -> 245 ms, 32 -> 235, 64 -> 232
+        prm->b_after_lo = std::min(v > 0 ? v : LP_B0, prm->bmax); // measured on configs[1] (bmax 64): 16 -> 245 ms, 32 -> 235, 64 -> 232
     } prm->guard = 1e-3;
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
@@ -106,15 +106,20 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.lo_req.reserve(n_pairs * sizeof(int)));
     int *h_active = A.h_active.as<int>(), *h_iter = h_active + G, *h_side = h_active + 2 * G; // h_side[2 * (g * SLOTS + k)] = {pairs not done, pairs handed back so far}
     for (int g = 0; g < G; g++) { h_active[g] = std::min(gsz, n_pairs - g * gsz); h_iter[g] = 0; }
+    // MP_PRIO (experiments): 1 = the round pipelines run at high priority (their CTAs take freed SM slots before the
+    // local optimisations' CTAs), 2 = the other way round, 0 = equal
+    static const int prio_mode = [] { const char *e = getenv("MP_PRIO"); return e ? atoi(e) : 0; }();
+    int prio_lo = 0, prio_hi = 0;
+    MP_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi)); // numerically lower = higher priority
     while ((int)c->gstream.size() < G) {
         cudaStream_t gs; cudaEvent_t ge;
-        MP_CUDA(cudaStreamCreateWithFlags(&gs, cudaStreamNonBlocking));
+        MP_CUDA(cudaStreamCreateWithPriority(&gs, cudaStreamNonBlocking, prio_mode == 1 ? prio_hi : prio_lo));
         MP_CUDA(cudaEventCreateWithFlags(&ge, cudaEventDisableTiming));
         c->gstream.push_back(gs); c->gev.push_back(ge);
     }
     while ((int)c->sstream.size() < NSIDE) {
         cudaStream_t gs;
-        MP_CUDA(cudaStreamCreateWithFlags(&gs, cudaStreamNonBlocking));
+        MP_CUDA(cudaStreamCreateWithPriority(&gs, cudaStreamNonBlocking, prio_mode == 2 ? prio_hi : prio_lo));
         c->sstream.push_back(gs);
     }
     while ((int)c->sev.size() < G * SLOTS) {
@@ -386,7 +391,7 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
 }
 int mp_set_batch(mp_ctx *c, int iterations) {
     using namespace mp;
-    if (!c || iterations < 0 || iterations > LP_BMAX) return fail(MP_ERR_ARG, "mp_set_batch: 0 (default) .. 64");
+    if (!c || iterations < 0 || iterations > LP_BMAX) return fail(MP_ERR_ARG, "mp_set_batch: 0 (default) .. 256");
     c->batch_override = iterations;
     return MP_OK;
 }

@@ -21,7 +21,9 @@
 
 namespace mp {
 
-constexpr int LP_BMAX = 64;            // iterations per pair per round (upper bound)
+constexpr int LP_BMAX = 256;           // iterations per pair per round (upper bound; a pair starts at LP_B0 and doubles
+                                       // its batch after every round without a new best model)
+constexpr int LP_B0 = 64, LP_BDEF = 128; // measured on configs[1]: cap 64 -> 179-185 ms, 128 -> 178-181, 256 -> 183-187
 constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
 constexpr int LP_THREADS = 128;        // decide_kernel CTA
 constexpr int LP_CTAS_PER_SM = 2;
@@ -31,7 +33,8 @@ struct LoopParams {
     mp_options opt;
     mp_config cfg;
     int n_pairs, bmax;
-    int b_after_lo; // batch length of the first round after a local optimisation (doubles every round up to bmax)
+    int b_after_lo; // batch length of the first round and of the first round after a local optimisation (doubles every
+                    // quiet round up to bmax)
     double guard; // relative guard band of the fp32 score filter
 };
 

@@ -24,7 +24,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
             if (S.sizes[s][t] > pc.n) { S.prior[s] = 0.0; break; }
     S.phase = (S.prior[0] > 0.0 || S.prior[1] > 0.0) ? PH_ITER : PH_DONE;
     S.pre_done = prm.opt.lo_starting_iterations == 0 ? 1 : 0;
-    S.B = prm.bmax; S.batch_len = 0; S.it = 0; S.total = 0; S.broke = 0;
+    S.B = prm.b_after_lo; S.batch_len = 0; S.it = 0; S.total = 0; S.broke = 0;
     S.iters[0] = S.iters[1] = 0;
     const unsigned c = prm.opt.max_num_iterations_per_solver > prm.opt.min_num_iterations
                            ? prm.opt.max_num_iterations_per_solver : prm.opt.min_num_iterations;
@@ -49,7 +49,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
 // generator rings far enough for the whole batch and copy the raw words the batch can
 // consume into shared-memory windows; lane 0 then draws sequentially from the windows
 // (the draws of one stream are inherently sequential: rejection sampling).
-constexpr int SMP_WARPS = 4, SMP_WIN_A = 20 * LP_BMAX, SMP_WIN_B = 2 * LP_BMAX + 32;
+constexpr int SMP_WARPS = 2, SMP_WIN_A = 20 * LP_BMAX, SMP_WIN_B = 2 * LP_BMAX + 32;
 
 __device__ inline void warp_fill_window(MtStream *g, uint32_t *win, int need, int lane) {
     while (g->gen < g->pos + (unsigned long long)need) mt_refill(g, lane, 32, [] { __syncwarp(); });
@@ -86,15 +86,29 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
     const unsigned lo_start = prm.opt.lo_starting_iterations;
     unsigned len = (unsigned)S.B < max_it - S.it ? (unsigned)S.B : max_it - S.it;
     if (S.it < lo_start && len > lo_start - S.it) len = lo_start - S.it; // a batch never straddles lo_start
-    warp_fill_window(A, winA[warp], SMP_WIN_A, lane);
-    warp_fill_window(B, winB[warp], SMP_WIN_B, lane);
+    {
+        // iterations past the termination test of hybrid_ransac.h:169 are speculated for nothing: cut the batch at the
+        // expected number of iterations until a solver reaches its cap (+10 % + 4; any length gives the same result)
+        const double ps = S.prior[0] + S.prior[1];
+        double est = 1e18;
+        for (int s = 0; s < 2; s++)
+            if (S.prior[s] > 0.0) {
+                const double left = S.cap[s] > S.iters[s] ? (double)(S.cap[s] - S.iters[s]) : 1.0;
+                est = fmin(est, left * ps / S.prior[s]);
+            }
+        est = est * 1.1 + 4.0;
+        if (est < (double)len) len = (unsigned)est;
+    }
+    const int needA = 20 * (int)len, needB = 2 * (int)len + 32; // words staged for this batch (the window spills to the ring)
+    warp_fill_window(A, winA[warp], needA, lane);
+    warp_fill_window(B, winB[warp], needB, lane);
     if (lane != 0) return;
-    MtWindow sa{A, winA[warp], A->pos, SMP_WIN_A, 0, false}, sb{B, winB[warp], B->pos, SMP_WIN_B, 0, false};
+    MtWindow sa{A, winA[warp], A->pos, needA, 0, false}, sb{B, winB[warp], B->pos, needB, 0, false};
     const double prior0 = S.prior[0], prior1 = S.prior[1];
     int sizes[2][3];
     for (int s = 0; s < 2; s++)
         for (int t = 0; t < 3; t++) sizes[s][t] = S.sizes[s][t];
-    unsigned long long mask1 = 0; // iterations that drew solver 1
+    int n1 = 0; // iterations that drew solver 1
     for (unsigned b = 0; b < len; b++) {
         const double u = mt_uniform_real_t(sb, prior0 + prior1);
         int s = -1;
@@ -115,15 +129,15 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
                 for (int i = 0; i < k; i++) W.idx[b][i] = tmp[i];
         }
         W.solver[b] = s;
-        if (s == 1) mask1 |= 1ull << b;
+        n1 += s;
         W.posA[b] = sa.position(); W.posB[b] = sb.position();
     }
     { // hand the samples to the minimal kernel, one list per solver
-        const int g = p / L.gsz, n1 = __popcll(mask1), n0 = (int)len - n1;
+        const int g = p / L.gsz, n0 = (int)len - n1;
         int o0 = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1 = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
         int *it0 = L.items + (size_t)first * LP_BMAX, *it1 = L.items + (size_t)(L.n_pairs + first) * LP_BMAX;
         for (unsigned b = 0; b < len; b++) {
-            if ((mask1 >> b) & 1ull) it1[o1++] = q * LP_BMAX + (int)b;
+            if (W.solver[b] == 1) it1[o1++] = q * LP_BMAX + (int)b;
             else it0[o0++] = q * LP_BMAX + (int)b;
         }
     }

@@ -11,7 +11,7 @@
 
 namespace mp {
 
-constexpr int MT_N = 624, MT_M = 397, MT_RING = 4 * MT_N;
+constexpr int MT_N = 624, MT_M = 397, MT_RING = 10 * MT_N; // >= 20 words x LP_BMAX iterations of a batch + 624
 
 struct alignas(128) MtStream { // line-aligned: rings of neighbouring pairs never share a cache line
     uint32_t x[MT_RING];

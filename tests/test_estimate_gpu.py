@@ -125,7 +125,7 @@ def test_schedule_invariance(ctx):
     pairs = [q[1] for q in ps]
     ref = None
     try:
-        for batch, groups in [(0, 0), (8, 1), (64, 5), (17, 24), (32, 2)]:
+        for batch, groups in [(0, 0), (8, 1), (64, 5), (17, 24), (32, 2), (256, 1), (128, 3)]:
             ctx.set_batch(batch); ctx.set_groups(groups)
             m, s, inl = ctx.estimate_batch(kind, pairs, opt, cfg)
             sig = [(x.num_iterations_total, tuple(x.num_iterations_per_solver), x.number_lo_iterations, x.best_solver_type,
