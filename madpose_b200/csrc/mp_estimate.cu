@@ -200,7 +200,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         if (serial) MP_CUDA(tick(0));
         sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
         if (serial) MP_CUDA(tick(1));
-        MP_CUDA(launch_minimal_batch(L, dprm, first, count, gs));
+        MP_CUDA(launch_minimal_batch(L, dprm, first, count, (long long)std::min(count, std::max(gr[g].act, 0)) * prm->bmax, gs));
         if (serial) MP_CUDA(tick(2));
         if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, first, count, tile_cap, smem, gs));
         else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, first, count, tile_cap, smem, gs));

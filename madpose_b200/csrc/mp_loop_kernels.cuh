@@ -49,7 +49,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
 // generator rings far enough for the whole batch and copy the raw words the batch can
 // consume into shared-memory windows; lane 0 then draws sequentially from the windows
 // (the draws of one stream are inherently sequential: rejection sampling).
-constexpr int SMP_WARPS = 2, SMP_WIN_A = 20 * LP_BMAX, SMP_WIN_B = 2 * LP_BMAX + 32;
+constexpr int SMP_WARPS = 2, SMP_WIN_A = 20 * LP_BMAX, SMP_WIN_B = 2 * LP_BMAX;
 
 __device__ inline void warp_fill_window(MtStream *g, uint32_t *win, int need, int lane) {
     while (g->gen < g->pos + (unsigned long long)need) mt_refill(g, lane, 32, [] { __syncwarp(); });
@@ -64,6 +64,7 @@ __device__ inline void warp_fill_window(MtStream *g, uint32_t *win, int need, in
 
 __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     __shared__ uint32_t winA[SMP_WARPS][SMP_WIN_A], winB[SMP_WARPS][SMP_WIN_B];
+    __shared__ unsigned char ssolver[SMP_WARPS][LP_BMAX];
     const LoopParams &prm = *prmp;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = blockIdx.x * SMP_WARPS + warp, p = first + q;
@@ -99,17 +100,22 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
         est = est * 1.1 + 4.0;
         if (est < (double)len) len = (unsigned)est;
     }
-    const int needA = 20 * (int)len, needB = 2 * (int)len + 32; // words staged for this batch (the window spills to the ring)
+    const int needA = 20 * (int)len, needB = 2 * (int)len; // words staged for this batch
     warp_fill_window(A, winA[warp], needA, lane);
     warp_fill_window(B, winB[warp], needB, lane);
-    if (lane != 0) return;
-    MtWindow sa{A, winA[warp], A->pos, needA, 0, false}, sb{B, winB[warp], B->pos, needB, 0, false};
+    const unsigned long long posA0 = A->pos, posB0 = B->pos;
     const double prior0 = S.prior[0], prior1 = S.prior[1];
-    int sizes[2][3];
+    int sizes[2][3], expect[2] = {0, 0}; // expect[s]: words of stream A one iteration of solver s takes without a retry
     for (int s = 0; s < 2; s++)
-        for (int t = 0; t < 3; t++) sizes[s][t] = S.sizes[s][t];
-    int n1 = 0; // iterations that drew solver 1
-    for (unsigned b = 0; b < len; b++) {
+        for (int t = 0; t < 3; t++) {
+            sizes[s][t] = S.sizes[s][t];
+            expect[s] += mt_draw_words(n, sizes[s][t]);
+        }
+    // stream B: the solver of every iteration; generate_canonical takes exactly two words, so iteration b reads
+    // words 2b, 2b + 1 of the window -- all iterations at once
+    unsigned char *sol = ssolver[warp];
+    for (unsigned b = lane; b < len; b += 32) {
+        MtWindowRO sb{winB[warp], needB, (int)(2 * b), false};
         const double u = mt_uniform_real_t(sb, prior0 + prior1);
         int s = -1;
         double c = 0;
@@ -120,28 +126,82 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
             if (u <= c) { s = k; break; }
         }
         if (s < 0) s = prior1 > 0.0 ? 1 : 0; // unreachable (u <= sum of priors)
+        sol[b] = (unsigned char)s;
+        W.solver[b] = s;
+        W.posB[b] = posB0 + 2ull * (b + 1);
+    }
+    __syncwarp();
+    // stream A: an iteration takes expect[s] words unless a draw repeats an index (or Lemire's method rejects a word).
+    // 32 iterations are drawn at once at the offsets that assumes; the iterations up to and including the first one
+    // that took a different number of words are right, the chunk restarts behind it with the true offset.
+    auto draw_iteration = [&](auto &src, int s, unsigned b) {
         int tmp[8], scratch[16];
         for (int t = 0; t < 3; t++) {
             const int k = sizes[s][t];
             if (k <= 0) continue;
-            mt_draw_sample_t(sa, n, k, tmp, scratch); // type 1 of solver 0 is drawn and discarded (quirk Q1)
+            mt_draw_sample_t(src, n, k, tmp, scratch); // type 1 of solver 0 is drawn and discarded (quirk Q1)
             if ((s == 0 && t == 0) || (s == 1 && t == 2))
                 for (int i = 0; i < k; i++) W.idx[b][i] = tmp[i];
         }
-        W.solver[b] = s;
-        n1 += s;
-        W.posA[b] = sa.position(); W.posB[b] = sb.position();
+    };
+    unsigned b0 = 0;
+    int o0 = 0; // words of stream A consumed by the iterations before b0
+    bool serial_rest = false;
+    while (b0 < len) {
+        const unsigned b = b0 + lane;
+        const bool on = b < len;
+        const int s = on ? sol[b] : 0, ex = on ? expect[s] : 0;
+        int pre = ex;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, pre, o);
+            if (lane >= o) pre += v;
+        }
+        const int start = o0 + pre - ex;
+        int used = ex;
+        bool bad = false;
+        if (on) {
+            MtWindowRO sa{winA[warp], needA, start, false};
+            draw_iteration(sa, s, b); // a wrong guess of `start` only writes W.idx[b], which the redo overwrites
+            used = sa.used - start; bad = sa.overflow;
+        }
+        const unsigned dev = __ballot_sync(0xffffffffu, on && (used != ex || bad));
+        const unsigned ovf = __ballot_sync(0xffffffffu, on && bad);
+        const int f = dev ? __ffs(dev) - 1 : 32;
+        if (on && (lane < f || (lane == f && !bad))) W.posA[b] = posA0 + (unsigned long long)(start + used);
+        if (f == 32) {
+            o0 += __shfl_sync(0xffffffffu, pre, 31);
+            b0 += 32;
+        } else {
+            const int st_f = __shfl_sync(0xffffffffu, start, f), us_f = __shfl_sync(0xffffffffu, used, f);
+            if ((ovf >> f) & 1u) { b0 += f; o0 = st_f; serial_rest = true; break; } // window used up: the rest in order
+            b0 += f + 1; o0 = st_f + us_f;
+        }
+        __syncwarp(); // the redo of an iteration (another lane) writes W.idx[b] after the wrong guess did
     }
+    __syncwarp();
+    if (lane != 0) return;
+    unsigned long long endA = posA0 + (unsigned long long)o0;
+    if (serial_rest) {
+        MtWindow sa{A, winA[warp], posA0, needA, o0, false}; // spills to the ring
+        for (unsigned b = b0; b < len; b++) {
+            draw_iteration(sa, (int)sol[b], b);
+            W.posA[b] = sa.position();
+        }
+        endA = sa.position();
+    }
+    int n1 = 0; // iterations that drew solver 1
+    for (unsigned b = 0; b < len; b++) n1 += sol[b];
     { // hand the samples to the minimal kernel, one list per solver
         const int g = p / L.gsz, n0 = (int)len - n1;
-        int o0 = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1 = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
+        int o0i = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1i = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
         int *it0 = L.items + (size_t)first * LP_BMAX, *it1 = L.items + (size_t)(L.n_pairs + first) * LP_BMAX;
         for (unsigned b = 0; b < len; b++) {
-            if (W.solver[b] == 1) it1[o1++] = q * LP_BMAX + (int)b;
-            else it0[o0++] = q * LP_BMAX + (int)b;
+            if (sol[b] == 1) it1[o1i++] = q * LP_BMAX + (int)b;
+            else it0[o0i++] = q * LP_BMAX + (int)b;
         }
     }
-    A->pos = sa.position(); B->pos = sb.position();
+    A->pos = endA; B->pos = posB0 + 2ull * len;
     S.batch_len = (int)len;
     W.blen = (int)len;
 }

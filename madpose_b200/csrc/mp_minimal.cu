@@ -109,12 +109,16 @@ __global__ void __launch_bounds__(64) minimal_pack_kernel(LoopBuffers L, const L
     W.count[b] = k;
 }
 
-cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, cudaStream_t s) {
-    minimal_batch_kernel<<<(count * LP_BMAX + 32 + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
+// items_bound: upper bound of the samples of this round (pairs of the group that are not done x batch cap): the item
+// and candidate lists are dense, so the grids only have to cover them (45000 empty CTAs cost 0.13 ms in a round that
+// has one pair left)
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, cudaStream_t s) {
+    const long long ib = items_bound > 0 ? items_bound : 1;
+    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
     // worst case of the candidate list: every sample of the round is a point-solver sample with LP_MM candidates; the
     // threads beyond the actual count exit at once
-    minimal_tail_kernel<<<(count * LP_BMAX * LP_MM + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
-    minimal_pack_kernel<<<(count * LP_BMAX + 63) / 64, 64, 0, s>>>(L, dprm, first, count);
+    minimal_tail_kernel<<<(unsigned)((ib * LP_MM + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
+    minimal_pack_kernel<<<(unsigned)((ib + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
     return cudaGetLastError();
 }
 

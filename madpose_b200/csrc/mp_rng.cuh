@@ -91,6 +91,19 @@ struct MtWindow {
     MP_HD unsigned long long position() const { return spilled ? s->pos : pos0 + (unsigned long long)used; }
 };
 
+// Read-only window for a thread that draws at a GUESSED offset next to other threads: never touches the stream; past
+// the end it flags `overflow` and hands out changing words so that the retry loops of the caller still end.
+struct MtWindowRO {
+    const uint32_t *w;
+    int cnt, used;
+    bool overflow;
+    MP_HD uint32_t next() {
+        if (used < cnt) return mt_temper(w[used++]);
+        overflow = true;
+        return 2654435761u * (uint32_t)(++used);
+    }
+};
+
 // std::uniform_int_distribution<int>(a, b) on a 32-bit engine (libstdc++ 13: Lemire's method)
 template <class Src> MP_HD int mt_uniform_int_t(Src &s, int a, int b) {
     const uint32_t range = (uint32_t)(b - a) + 1u; // never 0 here (b - a < 2^32 - 1)
@@ -150,6 +163,13 @@ template <class Src> MP_HD void mt_draw_sample_t(Src &s, int n, int k, int *out,
             }
         for (int i = 0; i < k; i++) out[i] = scratch[i];
     }
+}
+// words mt_draw_sample_t takes when no draw has to be repeated
+MP_HD int mt_draw_words(int n, int k) {
+    if (k <= 0) return 0;
+    const double coeff = (double)n / (double)(n - k);
+    if (coeff < 2.718281828459045235360287471352662498) return k;
+    return k != n ? n - 1 : 0;
 }
 MP_HD void mt_draw_sample(MtStream *s, int n, int k, int *out, int *scratch) {
     MtDirect d{s};
