@@ -154,7 +154,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     init_state_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(L, dprm);
     MP_CUDA(cudaGetLastError());
     int launches = 2;
-    int tile_cap = (c->smem_optin - 4096) / 32;
+    // dynamic tile + the kernel's static shared memory (candidate list of LP_BMAX * LP_MM shorts, barrier) <= opt-in limit
+    int tile_cap = (c->smem_optin - (int)(LP_BMAX * LP_MM * sizeof(unsigned short)) - 2048) / 32;
     tile_cap = std::min(tile_cap, (max_n + 31) / 32 * 32);
     tile_cap = tile_cap / 32 * 32;
     const size_t smem = (size_t)tile_cap * 32;

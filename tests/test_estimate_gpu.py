@@ -68,6 +68,17 @@ def test_estimate_matches_oracle(ctx, oracle, config, npairs):
         assert rot_err_deg(q[0]["gt"]["R"].reshape(9), m[:9]) < 2.0
 
 
+def test_large_pairs_multi_tile(ctx, oracle):
+    """Pairs with more matches than one shared-memory tile of the fused scoring kernel holds (~7000): the tile size is
+    what the static + dynamic shared memory of that kernel allows, and the scores are accumulated over the tiles."""
+    ps = [problem(0, p=i, n=9000 + 500 * i) for i in range(2)] + [problem(0, p=5, n=400)]
+    kind, opt, cfg = ps[0][0]["kind"], ps[0][2], ps[0][3]
+    pairs = [q[1] for q in ps]
+    mo, so, io = oracle.estimate_batch(kind, pairs, opt, cfg, threads=4)
+    mg, sg, ig = ctx.estimate_batch(kind, pairs, opt, cfg)
+    compare(oracle, kind, pairs, opt, cfg, mo, so, io, mg, sg, ig, min_identical=2)
+
+
 @pytest.mark.parametrize("kw", [dict(final_least_squares=0), dict(random_seed=7), dict(lo_starting_iterations=0),
                                 dict(num_lo_steps=1, num_lsq_iterations=2), dict(min_num_iterations=10, max_num_iterations=30),
                                 dict(max_num_iterations_per_solver=60)])
