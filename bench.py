@@ -219,10 +219,10 @@ def main():
             "decide_phase_gcycles": {k2: round(v / 1e9, 3) for k2, v in phase_cycles.items()},
             "roofline": {"bound": bound, "kernel": {"decide": "scan_kernel + lo_kernel (fp64 re-score, inliers, local optimisation / LM)"}.get(dom, dom), "achieved": ach, "peak": peak, "unit": "TFLOP/s",
                          "frac": ach / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE lo_kernel launch (750 CTAs, 6.3 ms), from the
+                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE lo_kernel launch (750 CTAs, 7.4 ms: 22.06 MB read + 1.02 MB written), from the last
                          # `ncu --set full` capture summarised in profiles/r1_whole_path_v3.md; the class is ALU / latency
                          # bound (3.5 GB/s), the figure only shows that nothing is re-read from HBM
-                         "traffic": 22.0e6 if dom == "decide" else None,
+                         "traffic": 23.08e6 if dom == "decide" else None,
                          "peak_source": "register-only FFMA / DFMA probes measured in this run (fp32 %.1f, fp64 %.1f TFLOP/s); "
                                         "MEASURED_PEAKS.json holds HBM and bf16 tensor peaks only" % (peak32, peak64),
                          "avg_launch_ms": {"score": score_ms_launch, "decide": decide_ms_launch},
