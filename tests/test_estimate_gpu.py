@@ -127,6 +127,21 @@ def test_rejects_unimplemented_flags(ctx):
         ctx.estimate_batch(0, [pair], opt, cfg)
 
 
+def test_knob_and_helper_argument_checks(ctx):
+    """Bad arguments come back as an error code + message, never as a launch."""
+    with pytest.raises(RuntimeError, match="mp_set_batch"):
+        ctx.set_batch(257)
+    with pytest.raises(RuntimeError, match="mp_set_batch"):
+        ctx.set_batch(-1)
+    with pytest.raises(RuntimeError, match="mp_set_groups"):
+        ctx.set_groups(-1)
+    ctx.set_batch(0); ctx.set_groups(0)
+    with pytest.raises(RuntimeError, match="mp_get_depths"):
+        ctx.get_depths((0, 0), np.ones((4, 4), np.float32), np.zeros((3, 2)))
+    with pytest.raises(ValueError):
+        ctx.pose_errors(np.zeros((2, 4, 4)), np.zeros((3, 3, 3)), np.zeros((2, 3)))
+
+
 def test_schedule_invariance(ctx):
     """The result of a pair must not depend on how the device loop is scheduled: iterations speculated per round
     (mp_set_batch), number of stream groups (mp_set_groups; 1 = everything on one stream), i.e. on which round a pair
