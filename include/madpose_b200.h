@@ -20,7 +20,10 @@ enum { MP_OK = 0, MP_ERR_ARG = -1, MP_ERR_NO_DEVICE = -2, MP_ERR_CUDA = -3, MP_E
 
 /* estimator kind: which of the three Python entry points the call serves
  * (bindings.cpp:169-174) */
-enum { MP_KIND_CALIBRATED = 0, MP_KIND_SHARED_FOCAL = 1, MP_KIND_TWO_FOCAL = 2 };
+enum { MP_KIND_CALIBRATED = 0, MP_KIND_SHARED_FOCAL = 1, MP_KIND_TWO_FOCAL = 2,
+       /* HybridEstimatePoseAndScale (bindings.cpp:167-168, hybrid_pose_estimator.cpp:37-63): the calibrated estimator
+        * without offsets; min_depth is ignored, the returned offsets are 0 */
+       MP_KIND_SCALE_ONLY = 3 };
 
 /* madpose.HybridLORansacOptions: ExtendedHybridLORansacOptions
  * (src/hybrid_ransac.h:17-25) over ransac_lib::HybridLORansacOptions
@@ -130,6 +133,13 @@ int mp_set_groups(mp_ctx *ctx, int groups);
 /* Upper bound of the RANSAC iterations speculated per pair per round (1..256; 0 = default 128).  A pair starts with 64
  * and doubles its batch after every round that found no new best model.  Results do not depend on it. */
 int mp_set_batch(mp_ctx *ctx, int iterations);
+/* Parity forensics: with events_per_pair > 0 the next estimate calls record, per pair and in chronological order, one
+ * {iteration, score} record for every iteration whose best hypothesis was re-scored in fp64 and one {-1, score} record
+ * for every ScoreModel inside LocalOptimization / the final least squares (hybrid_ransac.h:383-482, 186-203).
+ * mp_read_trace copies pair `pair`'s records (2 doubles each) of the last call; *n_events = events the pair produced
+ * (those beyond events_per_pair were dropped).  Results never depend on tracing. */
+int mp_set_trace(mp_ctx *ctx, int events_per_pair);
+int mp_read_trace(mp_ctx *ctx, int pair, double *out, int cap_events, int *n_events);
 /* profiling aid: SM-clock cycles (one thread per pair's CTA, summed over pairs) the decide kernel spent in
  * {sequential scan, GetInliers, fp64 ScoreModel, LM evaluation, LM solves total, shuffles, un-flatten, LO total} */
 int mp_last_phase_cycles(mp_ctx *ctx, unsigned long long *cycles8);
@@ -166,12 +176,30 @@ int mp_inliers(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt
 int mp_minimal_solve_batch(mp_ctx *ctx, int kind, int solver_idx, const mp_pair *pair, const mp_options *opt,
                            const mp_config *cfg, int n_samples, const int32_t *sample_idx, mp_model *out_models,
                            int32_t *out_counts);
+/* The stand-alone solver functions of the Python module (bindings.cpp:157-166) on n_samples explicit samples:
+ * solve_scale_and_shift{,_shared_focal,_two_focal} (solver.cpp:35-125, 127-293, 295-480) -> out_sols, and
+ * solve_scale_shift_pose{,_shared_focal,_two_focal} (solver.cpp:482-534, 682-739, 986-1043, scale_on_x = false)
+ * -> out_models.  kind 0: 3 points, kinds 1/2: 4 points (NP).  x_homo / y_homo: per sample a 3 x NP row-major matrix
+ * whose COLUMNS are homogeneous points (the reference's Eigen::Matrix3d / Matrix3x4d as numpy passes it);
+ * depth_x / depth_y: per sample NP depths.  out_sols: per sample 8 rows of 6 doubles (1, b1, a2, b2*a2, f1, f2)
+ * (calibrated: f = 1; shared focal: f1 == f2), out_nsols rows valid.  out_models: per sample 8 models with
+ * scale = a2, offset0 = b1, offset1 = b2*a2 (the wrappers' convention, no min-depth filter), out_nmodels valid.
+ * Any of the four outputs may be NULL. */
+int mp_solve_affine(mp_ctx *ctx, int kind, int n_samples, const double *x_homo, const double *y_homo,
+                    const double *depth_x, const double *depth_y, double *out_sols, int32_t *out_nsols,
+                    mp_model *out_models, int32_t *out_nmodels);
+/* estimate_scale_and_pose (solver.cpp:5-33, bindings.cpp:156): weighted Umeyama Y ~ scale R X + t.
+ * X, Y: 3 x n row-major (columns = points), W: n weights.  out: R, t, scale (offsets 0, focals 1). */
+int mp_estimate_scale_and_pose(mp_ctx *ctx, int n, const double *X, const double *Y, const double *W, mp_model *out);
 /* NonMinimalSolver / LeastSquares (optimizer.h:9-131,247-499): one LM problem per
  * entry; problem j uses indices idx[off[3j+t] .. off[3j+t+1]) for data type t.
- * out_info: per problem {iterations, termination, initial_cost, final_cost} as doubles. */
+ * out_info: per problem {iterations, termination, initial_cost, final_cost} as doubles.
+ * nonminimal: 1 = the call is NonMinimalSolver, 0 = LeastSquares; they differ only in how EstimatorConfig.use_shift
+ * reaches the optimiser (calibrated: both; shared focal: NonMinimalSolver only,
+ * hybrid_pose_shared_focal_estimator.cpp:149; two focal: never). */
 int mp_lm_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
                 int n_problems, const mp_model *start, const int32_t *idx, const int32_t *off, mp_model *out_models,
-                double *out_info);
+                double *out_info, int nonminimal);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libmadpose_b200.so")
 
-KIND_CALIBRATED, KIND_SHARED_FOCAL, KIND_TWO_FOCAL = 0, 1, 2
+KIND_CALIBRATED, KIND_SHARED_FOCAL, KIND_TWO_FOCAL, KIND_SCALE_ONLY = 0, 1, 2, 3
 MODEL_DOUBLES = 17
 _dp = C.POINTER(C.c_double)
 
@@ -124,6 +124,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
     "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
+    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace",
 ]
 
 
@@ -229,14 +230,44 @@ class Context:
         """samples: (n_samples, k) int32.  Returns a list of (count, 17) arrays in the front-end's internal units."""
         idx = np.ascontiguousarray(samples, np.int32)
         ns = idx.shape[0]
-        mm = ([4, 8, 4] if solver_idx == 0 else [10, 15, 3])[kind]
+        mm = ([4, 8, 4, 4] if solver_idx == 0 else [10, 15, 3, 10])[kind]
         out = np.zeros((ns, mm, MODEL_DOUBLES)); cnt = np.zeros(ns, np.int32)
         self._check(self.lib.mp_minimal_solve_batch(self.ctx, kind, solver_idx, C.byref(pair), C.byref(opt), C.byref(cfg),
                                                     ns, idx.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
                                                     cnt.ctypes.data_as(C.c_void_p)))
         return [out[i, :cnt[i]].copy() for i in range(ns)]
 
-    def lm_batch(self, kind, pair, opt, cfg, starts, samples):
+    def set_trace(self, events_per_pair):
+        self._check(self.lib.mp_set_trace(self.ctx, int(events_per_pair)))
+
+    def read_trace(self, pair, cap=1 << 16):
+        """(events (k, 2) of the last estimate call for `pair`, number of events the pair produced)."""
+        out = np.zeros((cap, 2)); n = C.c_int()
+        self._check(self.lib.mp_read_trace(self.ctx, int(pair), out.ctypes.data_as(C.c_void_p), cap, C.byref(n)))
+        return out[:min(n.value, cap)].copy(), n.value
+
+    def solve_affine(self, kind, x_homo, y_homo, depth_x, depth_y):
+        """The stand-alone solver bindings on explicit samples: x_homo / y_homo (S, 3, NP) with COLUMNS = homogeneous
+        points (NP = 3 calibrated, 4 focal kinds), depths (S, NP).  Returns (sols, models): per sample an (ns, 6) array
+        of (1, b1, a2, b2 a2, f1, f2) = solve_scale_and_shift* and an (nm, 17) array = solve_scale_shift_pose*."""
+        npt = 3 if kind == 0 else 4
+        x = np.ascontiguousarray(x_homo, np.float64).reshape(-1, 3, npt); y = np.ascontiguousarray(y_homo, np.float64).reshape(-1, 3, npt)
+        dx = np.ascontiguousarray(depth_x, np.float64).reshape(-1, npt); dy = np.ascontiguousarray(depth_y, np.float64).reshape(-1, npt)
+        S = x.shape[0]
+        sols = np.zeros((S, 8, 6)); ns = np.zeros(S, np.int32); models = np.zeros((S, 8, MODEL_DOUBLES)); nm = np.zeros(S, np.int32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.mp_solve_affine(self.ctx, kind, S, vp(x), vp(y), vp(dx), vp(dy), vp(sols), vp(ns), vp(models), vp(nm)))
+        return [sols[i, :ns[i]].copy() for i in range(S)], [models[i, :nm[i]].copy() for i in range(S)]
+
+    def estimate_scale_and_pose(self, X, Y, W):
+        """estimate_scale_and_pose (solver.cpp:5-33): X, Y (3, n), W (n,) -> 17-double model (R, t, scale)."""
+        X = np.ascontiguousarray(X, np.float64); Y = np.ascontiguousarray(Y, np.float64); W = np.ascontiguousarray(W, np.float64)
+        out = np.zeros(MODEL_DOUBLES)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self._check(self.lib.mp_estimate_scale_and_pose(self.ctx, X.shape[1], vp(X), vp(Y), vp(W), vp(out)))
+        return out
+
+    def lm_batch(self, kind, pair, opt, cfg, starts, samples, nonminimal=False):
         """samples: per problem a list of 3 index arrays.  Returns (models (P,17), info (P,4))."""
         st = np.ascontiguousarray(starts, np.float64).reshape(-1, MODEL_DOUBLES)
         flat, off = [], [0]
@@ -248,7 +279,7 @@ class Context:
         self._check(self.lib.mp_lm_batch(self.ctx, kind, C.byref(pair), C.byref(opt), C.byref(cfg), st.shape[0],
                                          st.ctypes.data_as(C.c_void_p), idx.ctypes.data_as(C.c_void_p),
                                          off.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
-                                         info.ctypes.data_as(C.c_void_p)))
+                                         info.ctypes.data_as(C.c_void_p), int(nonminimal)))
         return out, info
 
     def estimate_batch(self, kind, pairs, opt, cfg, split=True):

@@ -2,8 +2,9 @@
 // /root/reference/src/bindings.cpp:22-175 -- same class, field and function names, same argument order,
 // same returned (model, statistics) tuples -- in front of the C ABI of include/madpose_b200.h.
 // Host C++ only (no Eigen, no CUDA headers): numpy in, numpy out, the GIL released around the device call.
-// Not provided on this path (they raise NotImplementedError): the scale-only estimator and the stand-alone
-// solver functions.
+// Everything the reference binds is bound here with a device body, including the scale-only estimator
+// HybridEstimatePoseAndScale / PoseAndScale (bindings.cpp:111-118,167-168) and the seven stand-alone solver
+// functions (bindings.cpp:156-166).
 #include <pybind11/iostream.h>
 #include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
@@ -98,6 +99,10 @@ struct PoseScaleOffset {
     }
 };
 struct PoseScaleOffsetSharedFocal : PoseScaleOffset { double focal = 1; };
+struct PoseAndScale { // pose.h:7-17: the base record, no offsets
+    PoseScaleOffset b;
+    double scale = 1;
+};
 struct PoseScaleOffsetTwoFocal : PoseScaleOffset { double focal0 = 1, focal1 = 1; };
 
 // ---- one device context per process (created on first use; MADPOSE_B200_DEVICE selects the GPU)
@@ -154,12 +159,12 @@ void run_batch(int kind, std::vector<PairIn> &in, const HybridLORansacOptions &o
         const py::ssize_t n = q.x0.shape(0);
         if (q.x1.shape(0) != n || q.d0.size() != n || q.d1.size() != n)
             throw std::invalid_argument("x0, x1, depth0, depth1 must have the same length"); // UB in the reference
-        if (q.min_depth.size() != 2) throw std::invalid_argument("min_depth must have 2 entries");
+        if (kind != MP_KIND_SCALE_ONLY && q.min_depth.size() != 2) throw std::invalid_argument("min_depth must have 2 entries");
         mp_pair &c = pairs[p];
         std::memset(&c, 0, sizeof(c));
         c.n = (int)n; c.x0 = q.x0.data(); c.x1 = q.x1.data(); c.d0 = q.d0.data(); c.d1 = q.d1.data();
-        c.min_depth[0] = q.min_depth.data()[0]; c.min_depth[1] = q.min_depth.data()[1];
-        if (kind == MP_KIND_CALIBRATED) {
+        if (kind != MP_KIND_SCALE_ONLY) { c.min_depth[0] = q.min_depth.data()[0]; c.min_depth[1] = q.min_depth.data()[1]; }
+        if (kind == MP_KIND_CALIBRATED || kind == MP_KIND_SCALE_ONLY) {
             if (q.A.size() != 9 || q.B.size() != 9) throw std::invalid_argument("K0 and K1 must be 3x3");
             std::memcpy(c.K0, q.A.data(), 72); std::memcpy(c.K1, q.B.data(), 72);
         } else {
@@ -209,6 +214,70 @@ template <> PoseScaleOffsetTwoFocal to_py<PoseScaleOffsetTwoFocal>(int, const mp
     PoseScaleOffsetTwoFocal r; r.from_model(m); r.focal0 = m.focal0; r.focal1 = m.focal1; return r;
 }
 
+template <> PoseAndScale to_py<PoseAndScale>(int, const mp_model &m) { PoseAndScale r; r.b.from_model(m); r.scale = m.scale; return r; }
+
+// ---- the stand-alone solver functions (bindings.cpp:156-166) through mp_solve_affine / mp_estimate_scale_and_pose
+void check_sample(int kind, const darray &x, const darray &y, const darray &dx, const darray &dy) {
+    const py::ssize_t np_ = kind == MP_KIND_CALIBRATED ? 3 : 4;
+    if (x.ndim() != 2 || x.shape(0) != 3 || x.shape(1) != np_ || y.ndim() != 2 || y.shape(0) != 3 || y.shape(1) != np_)
+        throw std::invalid_argument(kind == MP_KIND_CALIBRATED ? "x_homo and y_homo must be 3x3 (columns = homogeneous points)"
+                                                                : "x_homo and y_homo must be 3x4 (columns = homogeneous points)");
+    if (dx.size() != np_ || dy.size() != np_) throw std::invalid_argument("depth_x and depth_y must have one entry per point");
+}
+void solve_affine(int kind, const darray &x, const darray &y, const darray &dx, const darray &dy, double *sols, int *ns,
+                  mp_model *models, int *nm) {
+    check_sample(kind, x, y, dx, dy);
+    int rc;
+    std::string err;
+    {
+        py::gil_scoped_release nogil;
+        std::lock_guard<std::mutex> lock(g_mu);
+        rc = mp_solve_affine(context(), kind, 1, x.data(), y.data(), dx.data(), dy.data(), sols, ns, models, nm);
+        if (rc != MP_OK) err = mp_last_error();
+    }
+    if (rc == MP_ERR_ARG) throw std::invalid_argument("madpose_b200: " + err);
+    if (rc != MP_OK) throw std::runtime_error("madpose_b200: " + err);
+}
+// solve_scale_and_shift* -> list of (1, b1, a2, b2 a2[, f | f1, f2]) vectors (solver.cpp:117-121, 285-289, 472-477)
+template <int KIND> std::vector<py::array> solve_raw(darray x, darray y, darray dx, darray dy) {
+    double sols[48];
+    int ns = 0;
+    solve_affine(KIND, x, y, dx, dy, sols, &ns, nullptr, nullptr);
+    const int w = KIND == MP_KIND_CALIBRATED ? 4 : (KIND == MP_KIND_SHARED_FOCAL ? 5 : 6);
+    std::vector<py::array> out;
+    for (int q = 0; q < ns; q++) {
+        darray a(w);
+        for (int k = 0; k < w; k++) a.mutable_data()[k] = sols[6 * q + k];
+        out.push_back(a);
+    }
+    return out;
+}
+// solve_scale_shift_pose*_wrapper -> list of pose records (scale = a2, offset0 = b1, offset1 = b2 a2)
+template <class M, int KIND> std::vector<M> solve_pose(darray x, darray y, darray dx, darray dy) {
+    mp_model models[8];
+    int nm = 0;
+    solve_affine(KIND, x, y, dx, dy, nullptr, nullptr, models, &nm);
+    std::vector<M> out;
+    for (int q = 0; q < nm; q++) out.push_back(to_py<M>(KIND, models[q]));
+    return out;
+}
+PoseAndScale scale_and_pose(darray X, darray Y, darray W) {
+    if (X.ndim() != 2 || X.shape(0) != 3 || Y.ndim() != 2 || Y.shape(0) != 3 || X.shape(1) != Y.shape(1) || W.size() != X.shape(1))
+        throw std::invalid_argument("X and Y must be 3xN and W must have N entries");
+    mp_model m;
+    int rc;
+    std::string err;
+    {
+        py::gil_scoped_release nogil;
+        std::lock_guard<std::mutex> lock(g_mu);
+        rc = mp_estimate_scale_and_pose(context(), (int)X.shape(1), X.data(), Y.data(), W.data(), &m);
+        if (rc != MP_OK) err = mp_last_error();
+    }
+    if (rc == MP_ERR_ARG) throw std::invalid_argument("madpose_b200: " + err);
+    if (rc != MP_OK) throw std::runtime_error("madpose_b200: " + err);
+    return to_py<PoseAndScale>(0, m);
+}
+
 template <class M, int KIND>
 std::pair<M, HybridRansacStatistics> estimate_one(darray x0, darray x1, darray d0, darray d1, darray min_depth, darray A,
                                                   darray B, const HybridLORansacOptions &options, const EstimatorConfig &cfg) {
@@ -239,10 +308,18 @@ std::vector<std::pair<M, HybridRansacStatistics>> estimate_many(std::vector<darr
     return out;
 }
 
-[[noreturn]] void not_on_path(const char *name) {
-    PyErr_SetString(PyExc_NotImplementedError,
-                    (std::string(name) + " is outside the B200 hot path of madpose_b200 (SURVEY.md 8f); there is no CPU fallback").c_str());
-    throw py::error_already_set();
+// HybridEstimatePoseAndScale (bindings.cpp:167-168): no min_depth argument
+std::pair<PoseAndScale, HybridRansacStatistics> estimate_scale_only(darray x0, darray x1, darray d0, darray d1, darray K0, darray K1,
+                                                                    const HybridLORansacOptions &options, const EstimatorConfig &cfg) {
+    return estimate_one<PoseAndScale, MP_KIND_SCALE_ONLY>(x0, x1, d0, d1, darray(), K0, K1, options, cfg);
+}
+std::vector<std::pair<PoseAndScale, HybridRansacStatistics>> estimate_scale_only_many(std::vector<darray> x0, std::vector<darray> x1,
+                                                                                      std::vector<darray> d0, std::vector<darray> d1,
+                                                                                      std::vector<darray> K0, std::vector<darray> K1,
+                                                                                      const HybridLORansacOptions &options,
+                                                                                      const EstimatorConfig &cfg) {
+    std::vector<darray> md(x0.size());
+    return estimate_many<PoseAndScale, MP_KIND_SCALE_ONLY>(x0, x1, d0, d1, md, K0, K1, options, cfg);
 }
 
 template <class M> void bind_pose_common(py::class_<M> &c) {
@@ -330,6 +407,14 @@ PYBIND11_MODULE(_madpose, m) {
         .def_readwrite("ceres_use_nonmonotonic_steps", &EstimatorConfig::ceres_use_nonmonotonic_steps)
         .def_readwrite("ceres_num_threads", &EstimatorConfig::ceres_num_threads);
 
+    py::class_<PoseAndScale>(m, "PoseAndScale")
+        .def(py::init<>())
+        .def(py::init([](const darray &p, double s) { PoseAndScale r; r.b.set(p); r.scale = s; return r; }))
+        .def(py::init([](const darray &R, const darray &t, double s) { PoseAndScale r; r.b.set(R, t); r.scale = s; return r; }))
+        .def_property("pose", [](const PoseAndScale &m) { return m.b.get_pose(); }, [](PoseAndScale &m, const darray &p) { m.b.set(p); })
+        .def_readwrite("scale", &PoseAndScale::scale)
+        .def("R", [](const PoseAndScale &m) { return m.b.R(); })
+        .def("t", [](const PoseAndScale &m) { return m.b.t(); });
     py::class_<PoseScaleOffset> pso(m, "PoseScaleOffset");
     pso.def(py::init<>())
         .def(py::init([](const darray &p, double s, double o0, double o1) { PoseScaleOffset r; r.set(p); r.scale = s; r.offset0 = o0; r.offset1 = o1; return r; }))
@@ -362,10 +447,17 @@ PYBIND11_MODULE(_madpose, m) {
           "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig());
     m.def("HybridEstimatePoseScaleOffsetTwoFocalBatch", &estimate_many<PoseScaleOffsetTwoFocal, MP_KIND_TWO_FOCAL>, "x0"_a,
           "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig());
-    for (const char *name : {"HybridEstimatePoseAndScale", "estimate_scale_and_pose", "solve_scale_and_shift",
-                             "solve_scale_and_shift_shared_focal", "solve_scale_and_shift_two_focal", "solve_scale_shift_pose",
-                             "solve_scale_shift_pose_shared_focal", "solve_scale_shift_pose_two_focal"}) {
-        std::string nm = name;
-        m.def(name, [nm](py::args, py::kwargs) -> py::object { not_on_path(nm.c_str()); });
-    }
+    m.def("HybridEstimatePoseAndScale", &estimate_scale_only, "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "K0"_a, "K1"_a, "options"_a,
+          "est_config"_a = EstimatorConfig());
+    m.def("HybridEstimatePoseAndScaleBatch", &estimate_scale_only_many, "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "K0"_a, "K1"_a,
+          "options"_a, "est_config"_a = EstimatorConfig());
+    m.def("estimate_scale_and_pose", &scale_and_pose, "X"_a, "Y"_a, "W"_a);
+    m.def("solve_scale_and_shift", &solve_raw<MP_KIND_CALIBRATED>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);
+    m.def("solve_scale_and_shift_shared_focal", &solve_raw<MP_KIND_SHARED_FOCAL>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);
+    m.def("solve_scale_and_shift_two_focal", &solve_raw<MP_KIND_TWO_FOCAL>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);
+    m.def("solve_scale_shift_pose", &solve_pose<PoseScaleOffset, MP_KIND_CALIBRATED>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);
+    m.def("solve_scale_shift_pose_shared_focal", &solve_pose<PoseScaleOffsetSharedFocal, MP_KIND_SHARED_FOCAL>, "x_homo"_a, "y_homo"_a,
+          "depth_x"_a, "depth_y"_a);
+    m.def("solve_scale_shift_pose_two_focal", &solve_pose<PoseScaleOffsetTwoFocal, MP_KIND_TWO_FOCAL>, "x_homo"_a, "y_homo"_a,
+          "depth_x"_a, "depth_y"_a);
 }

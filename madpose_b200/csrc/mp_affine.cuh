@@ -215,4 +215,31 @@ template <int NP> MP_HD bool kabsch(const double (*X)[3], const double (*Y)[3], 
     return true;
 }
 
+// estimate_scale_and_pose (solver.cpp:5-33): weighted Umeyama, Y ~ scale R X + t.  Centroids and covariance are
+// weighted; the scale is the unweighted ratio sum(Yc . R Xc) / sum(R Xc . R Xc) (solver.cpp:28-29).
+MP_HD bool umeyama(int n, const double (*X)[3], const double (*Y)[3], const double *W, double *R, double *t, double *scale) {
+    double cx[3] = {0, 0, 0}, cy[3] = {0, 0, 0}, S[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, ws = 0;
+    for (int i = 0; i < n; i++) {
+        ws += W[i];
+        for (int k = 0; k < 3; k++) { cx[k] += X[i][k] * W[i]; cy[k] += Y[i][k] * W[i]; }
+    }
+    for (int k = 0; k < 3; k++) { cx[k] /= ws; cy[k] /= ws; }
+    for (int i = 0; i < n; i++)
+        for (int a = 0; a < 3; a++)
+            for (int b = 0; b < 3; b++) S[3 * a + b] += (Y[i][a] - cy[a]) * W[i] * (X[i][b] - cx[b]);
+    if (!procrustes_rotation(S, R)) return false;
+    double num = 0, den = 0;
+    for (int i = 0; i < n; i++) {
+        const double xc[3] = {X[i][0] - cx[0], X[i][1] - cx[1], X[i][2] - cx[2]};
+        double xr[3];
+        mat3_vecp(R, xc, xr);
+        for (int k = 0; k < 3; k++) { num += (Y[i][k] - cy[k]) * xr[k]; den += xr[k] * xr[k]; }
+    }
+    *scale = num / den;
+    double Rc[3];
+    mat3_vecp(R, cx, Rc);
+    for (int k = 0; k < 3; k++) t[k] = cy[k] - *scale * Rc[k];
+    return true;
+}
+
 } // namespace mp

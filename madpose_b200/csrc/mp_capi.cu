@@ -17,7 +17,12 @@ namespace mp {
 // staging blocks of all pairs are resident.
 int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt) {
     if (!c || !pairs || !opt || n_pairs <= 0) return fail(MP_ERR_ARG, "upload_pairs: bad arguments");
-    if (kind < 0 || kind > 2) return fail(MP_ERR_ARG, "kind must be 0, 1 or 2");
+    if (kind < 0 || kind > 3) return fail(MP_ERR_ARG, "kind must be 0 (calibrated), 1 (shared focal), 2 (two focal) or 3 (scale only)");
+    // whatever was resident is overwritten below: a failed or per-subsystem upload must not leave mp_estimate_resident
+    // believing the previous batch is still there
+    c->resident_pairs = 0; c->resident_kind = -1;
+    const int scale_only = kind == MP_KIND_SCALE_ONLY ? 1 : 0;
+    if (scale_only) kind = CALIB; // same kernels; PairConst::scale_only switches the solver 0 / guards / LM differences
     c->off.assign(n_pairs + 1, 0);
     c->off32.assign(n_pairs + 1, 0);
     for (int p = 0; p < n_pairs; p++) {
@@ -48,10 +53,10 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
             std::memcpy(c->h_d0.as<double>() + c->off[p], q.d0, n * sizeof(double));
             std::memcpy(c->h_d1.as<double>() + c->off[p], q.d1, n * sizeof(double));
             PairRaw &r = raw[p];
-            r.n = q.n; r.kind = kind; r.off = c->off[p]; r.off32 = c->off32[p];
+            r.n = q.n; r.kind = kind; r.off = c->off[p]; r.off32 = c->off32[p]; r.scale_only = scale_only; r.pad_ = 0;
             std::memcpy(r.K0, q.K0, sizeof(r.K0)); std::memcpy(r.K1, q.K1, sizeof(r.K1));
             for (int k = 0; k < 2; k++) {
-                r.pp0[k] = q.pp0[k]; r.pp1[k] = q.pp1[k]; r.min_depth[k] = q.min_depth[k];
+                r.pp0[k] = q.pp0[k]; r.pp1[k] = q.pp1[k]; r.min_depth[k] = scale_only ? 0.0 : q.min_depth[k];
                 r.thr[k] = opt->squared_inlier_thresholds[k]; r.w[k] = opt->data_type_weights[k];
             }
         }
@@ -85,6 +90,7 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
                                               c->d_m64.as<Match64>(), c->d_s32.as<float4>());
     MP_CUDA(cudaGetLastError());
     c->last_launches = 1;
+    for (int k = 0; k < 2; k++) { c->up_thr[k] = opt->squared_inlier_thresholds[k]; c->up_w[k] = opt->data_type_weights[k]; }
     return MP_OK;
 }
 
@@ -135,9 +141,10 @@ const char *mp_last_error(void) { return g_err.c_str(); }
 int mp_create(int device, mp_ctx **out) {
     if (!out) return fail(MP_ERR_ARG, "mp_create: out is null");
     *out = nullptr;
-    // the device loop keeps up to ~20 streams busy; the driver's default of 8 hardware queues makes them wait on each
-    // other (measured: 646 -> 511 ms/step at 32 groups).  Only effective before the process creates its CUDA context.
-    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
+    // The device loop keeps up to ~20 streams busy and the driver's default of 8 hardware queues makes them wait on each
+    // other (measured: 646 -> 511 ms/step at 32 groups): CUDA_DEVICE_MAX_CONNECTIONS=32 is a CALLER-side setting that
+    // must be in the environment before the process creates its CUDA context; the library does not
+    // touch the environment.
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail(MP_ERR_NO_DEVICE, "no CUDA device: madpose_b200 has no CPU path");
@@ -282,7 +289,7 @@ int mp_score_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *o
     MP_CUDA(cudaEventRecord(c->ev[1], s));
     int launches = 1;
     if (s32) {
-        pack_hyps_kernel<<<(nm + 255) / 256, 256, 0, s>>>(kind, nm, c->d_models.as<Model>(), c->d_hyps.as<HypF>());
+        pack_hyps_kernel<<<(nm + 255) / 256, 256, 0, s>>>(kind == MP_KIND_SCALE_ONLY ? CALIB : kind, nm, c->d_models.as<Model>(), c->d_hyps.as<HypF>());
         int cap = (c->smem_optin - 2048) / 32;
         cap = std::min(cap, std::max(pair->n, 32));
         cap = (cap + 31) / 32 * 32;
@@ -296,7 +303,7 @@ int mp_score_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *o
                                             c->d_hyps.as<HypF>(), c->d_scores32.as<float>(), cap);
             return cudaGetLastError();
         };
-        if (kind == CALIB) MP_CUDA(launch(score_f32_kernel<CALIB>));
+        if (kind == CALIB || kind == MP_KIND_SCALE_ONLY) MP_CUDA(launch(score_f32_kernel<CALIB>));
         else if (kind == SHARED) MP_CUDA(launch(score_f32_kernel<SHARED>));
         else MP_CUDA(launch(score_f32_kernel<TWO>));
         launches += 2;

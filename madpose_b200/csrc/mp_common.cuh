@@ -50,6 +50,9 @@ struct PairConst {
     double loss_scale;   // sampson_loss_scale_ (calibrated), 1 otherwise
     double norm_scale;   // poselib::normalize_points scale (focal kinds), 1 otherwise
     double pp0[2], pp1[2];
+    int scale_only;      // 1: HybridEstimatePoseAndScale (hybrid_pose_estimator.cpp:37-63,297-442): kind == CALIB,
+                         // offsets absent, depth guards in the reprojection residuals (quirk Q16)
+    int pad_;
 };
 
 MP_HD void mat3_mul(const double *A, const double *B, double *C) {

@@ -40,7 +40,13 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     if (opt->num_lsq_iterations < 0 || opt->num_lo_steps < 0 || opt->min_sample_multiplicator < 0)
         return fail(MP_ERR_ARG, "negative LO option");
     if (c->resident_pairs <= 0) return fail(MP_ERR_ARG, "no resident batch: call mp_upload_batch first");
-    const int kind = c->resident_kind, n_pairs = c->resident_pairs;
+    // thresholds and weights are baked into the resident PairConst records by the front-end (A.1 rewrite): a resident
+    // run with other values would silently use the stale ones
+    for (int k = 0; k < 2; k++)
+        if (opt->squared_inlier_thresholds[k] != c->up_thr[k] || opt->data_type_weights[k] != c->up_w[k])
+            return fail(MP_ERR_ARG, "mp_estimate_resident: squared_inlier_thresholds / data_type_weights differ from the "
+                                    "ones the batch was uploaded with; upload again");
+    const int kind = c->resident_kind == MP_KIND_SCALE_ONLY ? CALIB : c->resident_kind, n_pairs = c->resident_pairs;
     cudaStream_t s = c->stream;
     if (record_start) MP_CUDA(cudaEventRecord(c->ev[0], s));
     const long long N = c->total_n;
@@ -147,6 +153,11 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.items = A.items.as<int>(); L.n_pairs = n_pairs;
     L.lo_req = A.lo_req.as<int>();
     L.gsz = gsz;
+    L.trace = nullptr; L.trace_cap = c->trace_cap;
+    if (c->trace_cap > 0) {
+        MP_CUDA(A.trace.reserve((size_t)n_pairs * c->trace_cap * 2 * sizeof(double)));
+        L.trace = A.trace.as<double>();
+    }
     L.clk = reinterpret_cast<unsigned long long *>(A.misc.as<char>());
     MP_CUDA(cudaMemsetAsync(L.clk, 0, 128, s));
     const LoopParams *dprm = A.prm.as<LoopParams>();
@@ -314,7 +325,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
 
 extern "C" {
 int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int n_problems,
-                const mp_model *start, const int32_t *idx, const int32_t *off, mp_model *out_models, double *out_info) {
+                const mp_model *start, const int32_t *idx, const int32_t *off, mp_model *out_models, double *out_info,
+                int nonminimal) {
     using namespace mp;
     if (!c || !pair || !opt || !cfg || !start || !idx || !off || !out_models || !out_info || n_problems <= 0)
         return fail(MP_ERR_ARG, "mp_lm_batch: bad arguments");
@@ -345,9 +357,10 @@ int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt,
     const Match64 *M = c->d_m64.as<Match64>();
     const LoopParams *dprm = A.prm.as<LoopParams>();
     double *d_info = c->d_scores64.as<double>();
-    if (kind == CALIB) MP_CUDA(launch_lm_kind<CALIB>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
-    else if (kind == SHARED) MP_CUDA(launch_lm_kind<SHARED>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
-    else MP_CUDA(launch_lm_kind<TWO>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, s));
+    const bool nm = nonminimal != 0;
+    if (kind == CALIB || kind == MP_KIND_SCALE_ONLY) MP_CUDA(launch_lm_kind<CALIB>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, nm, s));
+    else if (kind == SHARED) MP_CUDA(launch_lm_kind<SHARED>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, nm, s));
+    else MP_CUDA(launch_lm_kind<TWO>(pc, M, dprm, n_problems, d_start, d_idx, d_off, d_out, d_info, nm, s));
     MP_CUDA(cudaEventRecord(c->ev[1], s));
     MP_CUDA(cudaMemcpyAsync(out_models, d_out, n_problems * sizeof(Model), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(out_info, d_info, 4 * (size_t)n_problems * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -389,6 +402,25 @@ int mp_estimate_batch(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, co
     if (rc) return rc;
     c->resident_kind = kind; c->resident_pairs = n_pairs;
     return run_estimate(c, *static_cast<LoopAlloc *>(c->loop_alloc), opt, cfg, out_models, out_stats, out_inliers, false);
+}
+int mp_set_trace(mp_ctx *c, int events_per_pair) {
+    using namespace mp;
+    if (!c || events_per_pair < 0 || events_per_pair > (1 << 22)) return fail(MP_ERR_ARG, "mp_set_trace: 0 (off) .. 4194304 events per pair");
+    c->trace_cap = events_per_pair;
+    return MP_OK;
+}
+int mp_read_trace(mp_ctx *c, int pair, double *out, int cap_events, int *n_events) {
+    using namespace mp;
+    if (!c || !out || !n_events || pair < 0 || cap_events < 0) return fail(MP_ERR_ARG, "mp_read_trace: bad arguments");
+    LoopAlloc *A = static_cast<LoopAlloc *>(c->loop_alloc);
+    if (!A || c->trace_cap <= 0 || !A->trace.p || pair >= c->resident_pairs) return fail(MP_ERR_ARG, "mp_read_trace: no trace recorded for this pair (mp_set_trace before the estimate call)");
+    MP_CUDA(cudaSetDevice(c->device));
+    PairState st;
+    MP_CUDA(cudaMemcpy(&st, A->st.as<PairState>() + pair, sizeof(PairState), cudaMemcpyDeviceToHost));
+    *n_events = st.trace_n; // may exceed the capacity: the records beyond it were dropped
+    const int n = std::min(std::min(st.trace_n, c->trace_cap), cap_events);
+    if (n > 0) MP_CUDA(cudaMemcpy(out, A->trace.as<double>() + 2 * (size_t)pair * c->trace_cap, 2 * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+    return MP_OK;
 }
 int mp_set_batch(mp_ctx *c, int iterations) {
     using namespace mp;

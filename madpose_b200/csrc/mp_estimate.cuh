@@ -16,10 +16,10 @@ cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int
                            const int *caps, int round, cudaStream_t s);
 template <int KIND>
 cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopParams *dprm, int n_problems, const Model *start,
-                           const int *idx, const int *off, Model *out, double *info, cudaStream_t s);
+                           const int *idx, const int *off, Model *out, double *info, bool nonminimal, cudaStream_t s);
 
 struct LoopAlloc {
-    DevBuf st, wk, rngA, rngB, models, hyps, inl_best, inl_cur, flat, sample, misc, off3, caps, prm, out_models, out_stats, lo_req, items, cand, cand_ok;
+    DevBuf trace, st, wk, rngA, rngB, models, hyps, inl_best, inl_cur, flat, sample, misc, off3, caps, prm, out_models, out_stats, lo_req, items, cand, cand_ok;
     PinBuf h_off3, h_caps, h_prm, h_active, h_out;
 };
 

@@ -16,6 +16,7 @@ struct PairRaw {
     long long off32; // float4 offset of the fp32 staging block (multiple of 1)
     double K0[9], K1[9], pp0[2], pp1[2], min_depth[2];
     double thr[2], w[2]; // options.squared_inlier_thresholds / data_type_weights as given
+    int scale_only, pad_;
 };
 
 // poselib::normalize_points(x1, x2, T1, T2, true, false, true) [PoseLib v2.0.4, not in the
@@ -37,6 +38,11 @@ MP_HD void prep_match(const PairRaw &r, double ns, const double *K0i, const doub
         mat3_vec(K1i, o->x1x, o->x1y, 1.0, b);
         p[0] = (float)a[0]; p[1] = (float)a[1]; p[2] = (float)b[0]; p[3] = (float)b[1];
         q[0] = (float)d0; q[1] = (float)d1;
+        if (r.scale_only) { // hybrid_pose_estimator.cpp:386,398: a prior depth below 1e-2 makes the reprojection residual
+            // invalid whatever the model; a NaN depth in the fp32 record does that for free (fminf(NaN, thr) = thr)
+            if (d0 < 1e-2) q[0] = nanf("");
+            if (d1 < 1e-2) q[1] = nanf("");
+        }
         q[2] = (float)(1.0 / sqrt(a[0] * a[0] + a[1] * a[1] + 1.0));
         q[3] = (float)(1.0 / sqrt(b[0] * b[0] + b[1] * b[1] + 1.0));
     } else {
@@ -71,6 +77,7 @@ MP_HD void prep_constants(const PairRaw &r, double ns, PairConst *pcp) {
     }
     pc.norm_scale = ns;
     for (int k = 0; k < 2; k++) { pc.min_depth[k] = r.min_depth[k]; pc.pp0[k] = r.pp0[k]; pc.pp1[k] = r.pp1[k]; }
+    pc.scale_only = r.scale_only; pc.pad_ = 0;
 }
 
 } // namespace mp

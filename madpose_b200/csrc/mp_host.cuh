@@ -69,6 +69,7 @@ struct mp_ctx {
     double last_kernel_ms = 0, last_total_ms = 0;
     int last_launches = 0, last_rounds = 0;
     int resident_kind = -1, resident_pairs = 0;
+    double up_thr[2] = {0, 0}, up_w[2] = {0, 0}; // thresholds / weights the resident PairConst records were built with
     std::vector<cudaEvent_t> tick_ev;
     std::vector<int> tick_cls;
     int n_tick = 0;
@@ -76,6 +77,7 @@ struct mp_ctx {
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     int groups_override = 0, last_groups = 1; // 0 = automatic
+    int trace_cap = 0;                        // mp_set_trace: events kept per pair (0 = tracing off)
     int batch_override = 0;                   // speculated iterations per pair per round, 0 = LP_BMAX
     std::vector<cudaStream_t> gstream, sstream; // per-group round pipelines; side streams of the lo_kernel launches
     std::vector<cudaEvent_t> gev, sev;

@@ -97,6 +97,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
     C.cap = caps[p];
     C.inl_cur = L.inl_cur + 3 * pc.off;
     C.flat = L.flat + 2 * o3; C.base = C.flat + C.cap; C.sample = L.sample + 3 * o3; // o3 = sum of caps of earlier pairs
+    C.trace = L.trace ? L.trace + 2 * (size_t)p * L.trace_cap : nullptr; C.trace_cap = L.trace_cap;
     const unsigned lo_start = prm.opt.lo_starting_iterations;
     const unsigned max_it = prm.opt.max_num_iterations > prm.opt.min_num_iterations ? prm.opt.max_num_iterations
                                                                                    : prm.opt.min_num_iterations;
@@ -125,6 +126,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
                         if (threadIdx.x == 0) S.evals64 += n;
                         if (sc < loc) { loc = sc; loc_id = j; }
                     }
+                    if (threadIdx.x == 0 && loc_id >= 0) trace_event(C, (double)it, loc);
                     const bool newbest = loc_id >= 0 && loc < S.best_min_score;
                     if (newbest || it == lo_start) {
                         __syncthreads();
@@ -221,6 +223,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
     C.cap = caps[p];
     C.inl_cur = L.inl_cur + 3 * pc.off;
     C.flat = L.flat + 2 * o3; C.base = C.flat + C.cap; C.sample = L.sample + 3 * o3; // o3 = sum of caps of earlier pairs
+    C.trace = L.trace ? L.trace + 2 * (size_t)p * L.trace_cap : nullptr; C.trace_cap = L.trace_cap;
     const unsigned lo_start = prm.opt.lo_starting_iterations;
     const unsigned max_it = prm.opt.max_num_iterations > prm.opt.min_num_iterations ? prm.opt.max_num_iterations
                                                                                    : prm.opt.min_num_iterations;
@@ -326,7 +329,7 @@ cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int
 template <int KIND>
 __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lm_batch_kernel(const PairConst *pcp, const Match64 *M, const LoopParams *prmp,
                                                                   int n_problems, const Model *start, const int *idx,
-                                                                  const int *off, Model *out, double *info) {
+                                                                  const int *off, Model *out, double *info, bool nonminimal) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     const int j = blockIdx.x;
@@ -334,11 +337,11 @@ __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lm_batch_kernel(co
     __syncthreads();
     BlockCtx C;
     C.pc = pcp; C.M = M + pcp->off; C.prm = prmp; C.S = &S; C.rngB = nullptr; C.sh = &sh; C.cap = 0;
-    C.inl_cur = nullptr; C.flat = nullptr; C.base = nullptr; C.sample = nullptr;
+    C.inl_cur = nullptr; C.flat = nullptr; C.base = nullptr; C.sample = nullptr; C.trace = nullptr; C.trace_cap = 0;
     const int *l0 = idx + off[3 * j], *l1 = idx + off[3 * j + 1], *l2 = idx + off[3 * j + 2];
     const int n0 = off[3 * j + 1] - off[3 * j], n1 = off[3 * j + 2] - off[3 * j + 1], n2 = off[3 * j + 3] - off[3 * j + 2];
     __shared__ LmInfo inf;
-    if (threadIdx.x == 0) { inf = LmInfo{0, 0, 0, 0}; sh.lm_go = lm_setup(*pcp, prmp->cfg, n0, n1, n2, &sh.lm_setup) ? 1 : 0; }
+    if (threadIdx.x == 0) { inf = LmInfo{0, 0, 0, 0}; sh.lm_go = lm_setup(*pcp, prmp->cfg, n0, n1, n2, &sh.lm_setup, nonminimal) ? 1 : 0; }
     __syncthreads();
     if (sh.lm_go) {
         BlockEval<KIND> ev;
@@ -353,8 +356,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lm_batch_kernel(co
 }
 template <int KIND>
 cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopParams *dprm, int n_problems, const Model *start,
-                           const int *idx, const int *off, Model *out, double *info, cudaStream_t s) {
-    lm_batch_kernel<KIND><<<n_problems, LP_THREADS, 0, s>>>(pc, M, dprm, n_problems, start, idx, off, out, info);
+                           const int *idx, const int *off, Model *out, double *info, bool nonminimal, cudaStream_t s) {
+    lm_batch_kernel<KIND><<<n_problems, LP_THREADS, 0, s>>>(pc, M, dprm, n_problems, start, idx, off, out, info, nonminimal);
     return cudaGetLastError();
 }
 

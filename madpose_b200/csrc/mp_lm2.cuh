@@ -27,7 +27,11 @@ struct LmSetup {
 
 // Guard + parameter activation + bounds.  n0,n1,n2 = sizes of the three index lists.
 // Returns false when the estimator's guard rejects the sample (model left untouched).
-MP_HD bool lm_setup(const PairConst &pc, const mp_config &cfg, int n0, int n1, int n2, LmSetup *L) {
+// nonminimal: the call is NonMinimalSolver (true) or LeastSquares (false).  EstimatorConfig::use_shift reaches the
+// optimiser only at hybrid_pose_estimator.cpp:206,281 (calibrated, both calls) and
+// hybrid_pose_shared_focal_estimator.cpp:149 (shared focal, NonMinimalSolver only); the scale-only optimiser
+// (optimizer.h:133-245) always holds the offsets constant and sets no offset bounds.
+MP_HD bool lm_setup(const PairConst &pc, const mp_config &cfg, int n0, int n1, int n2, LmSetup *L, bool nonminimal) {
     const int k0 = pc.kind == CALIB ? 3 : 4, k2 = pc.kind == CALIB ? 5 : (pc.kind == SHARED ? 6 : 7);
     if ((n0 < k0 && n1 < k0) || n2 < k2) return false;
     L->kind = pc.kind;
@@ -37,14 +41,16 @@ MP_HD bool lm_setup(const PairConst &pc, const mp_config &cfg, int n0, int n1, i
     const bool b0 = L->use_reproj && n0 > 0, b1 = L->use_reproj && n1 > 0, b2 = L->use_samp && n2 > 0;
     if (!b0 && !b1 && !b2) return false;
     bool act[LM_NT];
-    act[0] = b0 && cfg.use_shift; act[1] = act[2] = act[3] = act[4] = act[5] = act[6] = true;
-    act[7] = b1; act[8] = b1 && cfg.use_shift; act[9] = pc.kind != CALIB; act[10] = pc.kind == TWO;
+    const bool shift = pc.scale_only ? false
+                     : (pc.kind == CALIB ? cfg.use_shift != 0 : (pc.kind == SHARED ? (nonminimal ? cfg.use_shift != 0 : true) : true));
+    act[0] = b0 && shift; act[1] = act[2] = act[3] = act[4] = act[5] = act[6] = true;
+    act[7] = b1; act[8] = b1 && shift; act[9] = pc.kind != CALIB; act[10] = pc.kind == TWO;
     L->nt = 0;
     for (int s = 0; s < LM_NT; s++) L->slot[s] = act[s] ? L->nt++ : -1;
     for (int k = 0; k < LM_NA; k++) { L->has_lower[k] = false; L->lower[k] = 0; }
     if (b1) { L->has_lower[8] = true; L->lower[8] = 1e-2; }                                   // optimizer.h:79-81
-    if (cfg.min_depth_constraint && b0) { L->has_lower[0] = true; L->lower[0] = -pc.min_depth[0] + 1e-2; }
-    if (cfg.min_depth_constraint && b1) { L->has_lower[9] = true; L->lower[9] = -pc.min_depth[1] + 1e-2; }
+    if (!pc.scale_only && cfg.min_depth_constraint && b0) { L->has_lower[0] = true; L->lower[0] = -pc.min_depth[0] + 1e-2; }
+    if (!pc.scale_only && cfg.min_depth_constraint && b1) { L->has_lower[9] = true; L->lower[9] = -pc.min_depth[1] + 1e-2; }
     if (pc.kind == TWO) { L->has_lower[10] = L->has_lower[11] = true; L->lower[10] = L->lower[11] = 1e-6; }
     L->ftol = cfg.ceres_function_tolerance; L->gtol = cfg.ceres_gradient_tolerance; L->ptol = cfg.ceres_parameter_tolerance;
     L->max_it = (int)cfg.ceres_max_num_iterations;

@@ -54,6 +54,7 @@ struct alignas(128) PairState { // 128-byte aligned: no cache line is shared bet
     unsigned long long evals64, lm_blocks; // fp64 (model x match) evaluations; LM residual-block evaluations
     unsigned lm_solves, lm_iters;
     int sizes[2][3], non_min_sample_size, min_sample_size;
+    int trace_n, trace_pad_; // events written to LoopBuffers::trace so far (mp_set_trace)
     unsigned long long clk[16]; // SM-clock cycles of thread 0 per phase: 0 scan 1 inliers 2 score64 3 lm eval 4 lm driver 5 shuffle 6 unflatten 7 LO total
 };
 
@@ -94,6 +95,11 @@ struct LoopBuffers {
                     // (negated while an lo_kernel CTA owns the pair)
     int gsz;
     unsigned long long *clk; // [8] phase cycle totals over all pairs (profiling aid)
+    // parity forensics (mp_set_trace): per pair trace_cap records of 2 doubles, chronological:
+    //   {it, score}   an iteration whose best candidate was re-scored in fp64 (score = the local best)
+    //   {-1, score}   every ScoreModel inside LocalOptimization / the final least squares
+    double *trace;
+    int trace_cap;
 };
 
 // ---------------------------------------------------------------- block-level helpers

@@ -37,7 +37,17 @@ struct BlockCtx {
     int *inl_cur, *flat, *base, *sample; // global scratch of this pair
     int cap;               // capacity of flat / base and of each of the 3 sample lists
     BlockScratch *sh;
+    double *trace;         // this pair's trace records or nullptr
+    int trace_cap;
 };
+
+// thread 0 only
+__device__ inline void trace_event(const BlockCtx &C, double tag, double value) {
+    if (!C.trace) return;
+    const int k = C.S->trace_n;
+    if (k < C.trace_cap) { C.trace[2 * k] = tag; C.trace[2 * k + 1] = value; }
+    C.S->trace_n = k + 1;
+}
 
 // ---- collective evaluation of cost, J^T J, J^T r at sh->lm_x; the sums are left in sh->total
 template <int KIND> struct BlockEval {
@@ -144,10 +154,10 @@ template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, con
 
 // NonMinimalSolver / LeastSquares on explicit lists; *m is a shared-memory model.
 template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, int n0, const int *l1, int n1,
-                                              const int *l2, int n2, Model *m) {
+                                              const int *l2, int n2, Model *m, bool nonminimal = false) {
     BlockScratch *sh = C.sh;
     __syncthreads();
-    if (threadIdx.x == 0) sh->lm_go = lm_setup(*C.pc, C.prm->cfg, n0, n1, n2, &sh->lm_setup) ? 1 : 0;
+    if (threadIdx.x == 0) sh->lm_go = lm_setup(*C.pc, C.prm->cfg, n0, n1, n2, &sh->lm_setup, nonminimal) ? 1 : 0;
     __syncthreads();
     if (!sh->lm_go) return;
     BlockEval<KIND> ev;
@@ -355,7 +365,7 @@ __device__ inline double block_score_counted(const BlockCtx &C, const Model &m) 
     MP_CLK_BEGIN();
     const double s = block_score64(*C.pc, C.M, m, C.prm->cfg.score_type, C.sh->red);
     MP_CLK_END(C, 2);
-    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; }
+    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; trace_event(C, -1.0, s); }
     return s;
 }
 
@@ -367,7 +377,7 @@ __device__ inline double block_score_inliers(const BlockCtx &C, const Model &m, 
     __shared__ double sc_sh;
     block_inliers(*C.pc, C.M, m, thr_inl, C.inl_cur, C.sh->cnt, C.sh->wcnt, &sc_sh, C.prm->cfg.score_type, C.sh->red);
     MP_CLK_END(C, 1);
-    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; }
+    if (threadIdx.x == 0) { C.S->hyps_scored += 1; C.S->evals += C.pc->n; C.S->evals64 += C.pc->n; trace_event(C, -1.0, sc_sh); }
     return sc_sh;
 }
 
@@ -421,10 +431,10 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
         __syncthreads();
         block_shuffle_resize(C, nonmin, C.base, &sh->base_len);
         LmSetup Lg;
-        if (!lm_setup(pc, C.prm->cfg, s0, s1, s2, &Lg)) continue; // NonMinimalSolver returned 0
+        if (!lm_setup(pc, C.prm->cfg, s0, s1, s2, &Lg, true)) continue; // NonMinimalSolver returned 0
         if (threadIdx.x == 0) sh->m_lo = sh->m_init;
         __syncthreads();
-        block_lsq<KIND>(C, l0, s0, l1, s1, l2, s2, &sh->m_lo);
+        block_lsq<KIND>(C, l0, s0, l1, s1, l2, s2, &sh->m_lo, true);
         sc = block_score_inliers(C, sh->m_lo, pc.thr); // the inliers feed the fit below
         update_best(sc, &sh->m_lo);
         block_lsq_fit<KIND>(C, pc.thr, solver, &sh->m_lo, false, true);

@@ -10,27 +10,95 @@
 namespace mp {
 
 __device__ __noinline__ int minimal_solver_ni(const PairConst &pc, const Match64 *M, int solver_idx, const int *idx,
-                                              bool min_depth_on, Model *out, bool with_tail = true) {
-    return minimal_solver(pc, M, solver_idx, idx, min_depth_on, out, with_tail);
+                                              unsigned mflags, Model *out, bool with_tail = true) {
+    return minimal_solver(pc, M, solver_idx, idx, mflags, out, with_tail);
 }
-__device__ __noinline__ bool minimal_tail_ni(const PairConst &pc, const Match64 *M, const int *idx, bool min_depth_on, Model *m) {
-    if (pc.kind == CALIB) return minimal_points_tail<CALIB>(pc, M, idx, min_depth_on, m);
-    if (pc.kind == SHARED) return minimal_points_tail<SHARED>(pc, M, idx, min_depth_on, m);
-    return minimal_points_tail<TWO>(pc, M, idx, min_depth_on, m);
+__device__ __noinline__ bool minimal_tail_ni(const PairConst &pc, const Match64 *M, const int *idx, unsigned mflags, Model *m) {
+    if (pc.kind == CALIB) return minimal_points_tail<CALIB>(pc, M, idx, mflags, m);
+    if (pc.kind == SHARED) return minimal_points_tail<SHARED>(pc, M, idx, mflags, m);
+    return minimal_points_tail<TWO>(pc, M, idx, mflags, m);
 }
 
 // K1/K2 stand-alone: one thread per sample of one pair (mp_minimal_solve_batch)
 __global__ void __launch_bounds__(64) minimal_kernel(const PairConst *pcp, const Match64 *M, int solver_idx, int k,
-                                                     int n_samples, const int *idx, int min_depth_on, int max_models,
+                                                     int n_samples, const int *idx, unsigned mflags, int max_models,
                                                      Model *out, int *counts) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_samples) return;
     const PairConst &pc = *pcp;
     Model tmp[kMaxModelsAny];
-    int c = minimal_solver_ni(pc, M + pc.off, solver_idx, idx + (size_t)s * k, min_depth_on != 0, tmp);
+    int c = minimal_solver_ni(pc, M + pc.off, solver_idx, idx + (size_t)s * k, mflags, tmp);
     if (c > max_models) c = max_models;
     counts[s] = c;
     for (int j = 0; j < c; j++) out[(size_t)s * max_models + j] = tmp[j];
+}
+
+// ---- stand-alone solver bindings (bindings.cpp:156-166): one thread per explicit sample.
+// xh / yh: per sample a 3 x NP row-major matrix whose COLUMNS are the homogeneous points (the layout numpy hands to the
+// reference's Eigen::Matrix3d / Matrix3x4d arguments)
+template <int KIND> __device__ void affine_sample_solve(const double *xh, const double *yh, const double *dx, const double *dy,
+                                                        double *sols6, int *nsols, Model *models, int *nmodels) {
+    constexpr int NPT = KIND == CALIB ? 3 : 4;
+    double x0[NPT][3], x1[NPT][3], d0[NPT], d1[NPT];
+    for (int k = 0; k < NPT; k++) {
+        for (int c = 0; c < 3; c++) { x0[k][c] = xh[c * NPT + k]; x1[k][c] = yh[c * NPT + k]; }
+        d0[k] = dx[k]; d1[k] = dy[k];
+    }
+    AffSol sols[8];
+    int ns = 0;
+    Model tmp[8];
+    const int nm = affine_pose_models<KIND>(x0, x1, d0, d1, tmp, sols, &ns);
+    for (int q = 0; q < ns; q++) { // solver.cpp:117-121, 285-289, 472-477: (1, b1, a2, b2 a2[, f | f1, f2])
+        double *o = sols6 + 6 * q;
+        o[0] = 1.0; o[1] = sols[q].b1; o[2] = sols[q].a2; o[3] = sols[q].b2 * sols[q].a2; o[4] = sols[q].f1; o[5] = sols[q].f2;
+    }
+    *nsols = ns;
+    for (int q = 0; q < nm; q++) models[q] = tmp[q];
+    *nmodels = nm;
+}
+__global__ void __launch_bounds__(64) affine_solve_kernel(int kind, int n_samples, const double *xh, const double *yh, const double *dx,
+                                                          const double *dy, double *sols, int *nsols, Model *models, int *nmodels) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_samples) return;
+    const int np_ = kind == CALIB ? 3 : 4;
+    const double *a = xh + (size_t)s * 3 * np_, *b = yh + (size_t)s * 3 * np_, *c = dx + (size_t)s * np_, *d = dy + (size_t)s * np_;
+    if (kind == CALIB) affine_sample_solve<CALIB>(a, b, c, d, sols + (size_t)s * 48, nsols + s, models + (size_t)s * 8, nmodels + s);
+    else if (kind == SHARED) affine_sample_solve<SHARED>(a, b, c, d, sols + (size_t)s * 48, nsols + s, models + (size_t)s * 8, nmodels + s);
+    else affine_sample_solve<TWO>(a, b, c, d, sols + (size_t)s * 48, nsols + s, models + (size_t)s * 8, nmodels + s);
+}
+// estimate_scale_and_pose (solver.cpp:5-33): X, Y are 3 x n row-major (columns = points), W n weights; one thread
+__global__ void umeyama_kernel(int n, const double *X, const double *Y, const double *W, Model *out, int *ok) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    // two passes over the points straight from global memory (n is arbitrary)
+    double cx[3] = {0, 0, 0}, cy[3] = {0, 0, 0}, S[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, ws = 0;
+    for (int i = 0; i < n; i++) {
+        ws += W[i];
+        for (int k = 0; k < 3; k++) { cx[k] += X[k * n + i] * W[i]; cy[k] += Y[k * n + i] * W[i]; }
+    }
+    for (int k = 0; k < 3; k++) { cx[k] /= ws; cy[k] /= ws; }
+    for (int i = 0; i < n; i++)
+        for (int a = 0; a < 3; a++)
+            for (int b = 0; b < 3; b++) S[3 * a + b] += (Y[a * n + i] - cy[a]) * W[i] * (X[b * n + i] - cx[b]);
+    Model m;
+    m.o0 = 0; m.o1 = 0; m.f0 = 1; m.f1 = 1; m.scale = 1;
+    for (int k = 0; k < 9; k++) m.R[k] = 0;
+    for (int k = 0; k < 3; k++) m.t[k] = 0;
+    *ok = 0;
+    if (procrustes_rotation(S, m.R)) {
+        double num = 0, den = 0;
+        for (int i = 0; i < n; i++) {
+            const double xc[3] = {X[i] - cx[0], X[n + i] - cx[1], X[2 * n + i] - cx[2]};
+            double xr[3];
+            mat3_vecp(m.R, xc, xr);
+            for (int k = 0; k < 3; k++) { num += (Y[k * n + i] - cy[k]) * xr[k]; den += xr[k] * xr[k]; }
+        }
+        m.scale = num / den;
+        double Rc[3];
+        mat3_vecp(m.R, cx, Rc);
+        for (int k = 0; k < 3; k++) m.t[k] = cy[k] - m.scale * Rc[k];
+        *ok = 1;
+    }
+    *out = m;
 }
 
 // ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
@@ -51,7 +119,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
     const int solver = W.solver[b];
     // point-only solver: candidates only; their tail (triangulation, depth fits) runs in minimal_tail_kernel with one
     // thread per candidate, so that it does not serialise over lanes holding different numbers of candidates
-    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], prm.cfg.min_depth_constraint != 0, tmp, solver == 0);
+    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], minimal_flags(prm.cfg), tmp, solver == 0);
     W.count[b] = c;
     Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
     HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
@@ -80,7 +148,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_tail_kernel(LoopBuffe
     const PairWork &W = L.wk[p];
     Model *slot = L.models + ((size_t)p * LP_BMAX + b) * LP_MM + j;
     Model m = *slot;
-    const bool ok = minimal_tail_ni(pc, L.M + pc.off, W.idx[b], prm.cfg.min_depth_constraint != 0, &m);
+    const bool ok = minimal_tail_ni(pc, L.M + pc.off, W.idx[b], minimal_flags(prm.cfg), &m);
     if (ok) *slot = m;
     L.cand_ok[((size_t)p * LP_BMAX + b) * LP_MM + j] = ok ? 1 : 0;
 }
@@ -136,8 +204,9 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
     cudaStream_t s = c->stream;
     int rc = upload_pairs(c, kind, 1, pair, opt);
     if (rc) return rc;
-    const int k = solver_idx == 0 ? (kind == CALIB ? 3 : 4) : (kind == CALIB ? 5 : (kind == SHARED ? 6 : 7));
-    const int mm = solver_idx == 0 ? kMaxModelsAffine[kind] : kMaxModelsPoints[kind];
+    const int kk = kind == MP_KIND_SCALE_ONLY ? CALIB : kind;
+    const int k = solver_idx == 0 ? (kk == CALIB ? 3 : 4) : (kk == CALIB ? 5 : (kk == SHARED ? 6 : 7));
+    const int mm = solver_idx == 0 ? kMaxModelsAffine[kk] : kMaxModelsPoints[kk];
     for (size_t i = 0; i < (size_t)n_samples * k; i++)
         if (sample_idx[i] < 0 || sample_idx[i] >= pair->n) return fail(MP_ERR_ARG, "sample index out of range");
     MP_CUDA(c->d_idx.reserve((size_t)n_samples * k * sizeof(int)));
@@ -146,7 +215,7 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
     MP_CUDA(cudaMemcpyAsync(c->d_idx.p, sample_idx, (size_t)n_samples * k * sizeof(int), cudaMemcpyHostToDevice, s));
     MP_CUDA(cudaEventRecord(c->ev[0], s));
     minimal_kernel<<<(n_samples + 63) / 64, 64, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), solver_idx, k,
-                                                        n_samples, c->d_idx.as<int>(), cfg->min_depth_constraint, mm,
+                                                        n_samples, c->d_idx.as<int>(), minimal_flags(*cfg), mm,
                                                         c->d_models.as<Model>(), c->d_misc.as<int>());
     MP_CUDA(cudaGetLastError());
     MP_CUDA(cudaEventRecord(c->ev[1], s));
@@ -156,6 +225,62 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
     float ms = 0;
     MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
     c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 2;
+    return MP_OK;
+}
+
+int mp_solve_affine(mp_ctx *c, int kind, int n_samples, const double *x_homo, const double *y_homo, const double *depth_x,
+                    const double *depth_y, double *out_sols, int32_t *out_nsols, mp_model *out_models, int32_t *out_nmodels) {
+    using namespace mp;
+    if (!c || !x_homo || !y_homo || !depth_x || !depth_y || n_samples <= 0 || kind < 0 || kind > 2)
+        return fail(MP_ERR_ARG, "mp_solve_affine: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    const int np_ = kind == CALIB ? 3 : 4;
+    const size_t nx = (size_t)n_samples * 3 * np_, nd = (size_t)n_samples * np_;
+    MP_CUDA(c->d_work.reserve((2 * nx + 2 * nd + (size_t)n_samples * 48) * sizeof(double)));
+    MP_CUDA(c->d_models.reserve((size_t)n_samples * 8 * sizeof(Model)));
+    MP_CUDA(c->d_misc.reserve(2 * (size_t)n_samples * sizeof(int)));
+    double *dx = c->d_work.as<double>(), *dy = dx + nx, *dd0 = dy + nx, *dd1 = dd0 + nd, *dsol = dd1 + nd;
+    int *dn = c->d_misc.as<int>();
+    MP_CUDA(cudaMemcpyAsync(dx, x_homo, nx * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dy, y_homo, nx * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dd0, depth_x, nd * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dd1, depth_y, nd * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaEventRecord(c->ev[0], s));
+    affine_solve_kernel<<<(n_samples + 63) / 64, 64, 0, s>>>(kind, n_samples, dx, dy, dd0, dd1, dsol, dn, c->d_models.as<Model>(), dn + n_samples);
+    MP_CUDA(cudaGetLastError());
+    MP_CUDA(cudaEventRecord(c->ev[1], s));
+    if (out_sols) MP_CUDA(cudaMemcpyAsync(out_sols, dsol, (size_t)n_samples * 48 * sizeof(double), cudaMemcpyDeviceToHost, s));
+    if (out_nsols) MP_CUDA(cudaMemcpyAsync(out_nsols, dn, n_samples * sizeof(int), cudaMemcpyDeviceToHost, s));
+    if (out_models) MP_CUDA(cudaMemcpyAsync(out_models, c->d_models.p, (size_t)n_samples * 8 * sizeof(Model), cudaMemcpyDeviceToHost, s));
+    if (out_nmodels) MP_CUDA(cudaMemcpyAsync(out_nmodels, dn + n_samples, n_samples * sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    float ms = 0;
+    MP_CUDA(cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]));
+    c->last_kernel_ms = ms; c->last_total_ms = ms; c->last_launches = 1;
+    return MP_OK;
+}
+
+int mp_estimate_scale_and_pose(mp_ctx *c, int n, const double *X, const double *Y, const double *W, mp_model *out) {
+    using namespace mp;
+    if (!c || !X || !Y || !W || !out || n <= 0) return fail(MP_ERR_ARG, "mp_estimate_scale_and_pose: bad arguments");
+    MP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t s = c->stream;
+    MP_CUDA(c->d_work.reserve((size_t)n * 7 * sizeof(double)));
+    MP_CUDA(c->d_models.reserve(sizeof(Model)));
+    MP_CUDA(c->d_misc.reserve(sizeof(int)));
+    double *dX = c->d_work.as<double>(), *dY = dX + 3 * (size_t)n, *dW = dY + 3 * (size_t)n;
+    MP_CUDA(cudaMemcpyAsync(dX, X, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dY, Y, 3 * (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    MP_CUDA(cudaMemcpyAsync(dW, W, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    umeyama_kernel<<<1, 32, 0, s>>>(n, dX, dY, dW, c->d_models.as<Model>(), c->d_misc.as<int>());
+    MP_CUDA(cudaGetLastError());
+    int ok = 0;
+    MP_CUDA(cudaMemcpyAsync(out, c->d_models.p, sizeof(Model), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaMemcpyAsync(&ok, c->d_misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(cudaStreamSynchronize(s));
+    c->last_launches = 1;
+    if (!ok) return fail(MP_ERR_ARG, "mp_estimate_scale_and_pose: degenerate point set (rank of the covariance below 2)");
     return MP_OK;
 }
 }

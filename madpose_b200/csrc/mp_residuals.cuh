@@ -18,11 +18,11 @@ struct Eval64 {
     double K0i[9], K1i[9];
     double R[9], F[9];   // F = K1^-T [t]x R K0^-1 (focal kinds); E for calibrated is t x (R a)
     double o0, o1, scale, loss_scale;
-    int kind;
+    int kind, depth_guard;
 };
 
 MP_HD void make_eval64(const PairConst &pc, const Model &m, Eval64 *e) {
-    e->kind = pc.kind;
+    e->kind = pc.kind; e->depth_guard = pc.scale_only;
     if (pc.kind == CALIB) {
         for (int i = 0; i < 9; i++) { e->K0[i] = pc.K0[i]; e->K1[i] = pc.K1[i]; e->K0i[i] = pc.K0i[i]; e->K1i[i] = pc.K1i[i]; }
     } else {
@@ -55,7 +55,7 @@ MP_HD double eval64(const Eval64 &e, const Match64 &m, int t) {
         mat3_vec(e.M0, m.x0x, m.x0y, 1.0, u);
         double s = m.d0 + e.o0;
         mat3_vec(e.K1, s * u[0] + e.t[0], s * u[1] + e.t[1], s * u[2] + e.t[2], p);
-        if (p[2] < 1e-2) return DBL_MAX;
+        if (p[2] < 1e-2 || (e.depth_guard && m.d0 < 1e-2)) return DBL_MAX;
         double a = p[0] / p[2] - m.x1x, b = p[1] / p[2] - m.x1y;
         return a * a + b * b;
     }
@@ -64,7 +64,7 @@ MP_HD double eval64(const Eval64 &e, const Match64 &m, int t) {
         mat3_vec(e.M1, m.x1x, m.x1y, 1.0, w);
         double s = (m.d1 + e.o1) * e.scale;
         mat3_vec(e.K0, s * w[0] + e.v1[0], s * w[1] + e.v1[1], s * w[2] + e.v1[2], p);
-        if (p[2] < 1e-2) return DBL_MAX;
+        if (p[2] < 1e-2 || (e.depth_guard && m.d1 < 1e-2)) return DBL_MAX;
         double a = p[0] / p[2] - m.x0x, b = p[1] / p[2] - m.x0y;
         return a * a + b * b;
     }

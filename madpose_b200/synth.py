@@ -18,9 +18,9 @@ def _rot(axis, ang):
     return np.eye(3) + np.sin(ang) * K + (1 - np.cos(ang)) * (K @ K)
 
 
-def make_pair(config, p, n=None, outlier_ratio=None):
+def make_pair(config, p, n=None, outlier_ratio=None, zero_offsets=False):
     """Returns a dict with x0,x1 (n,2), d0,d1 (n,), min_depth, K0,K1, pp0,pp1, kind, gt."""
-    rng = np.random.Generator(np.random.PCG64(10_000 * (config + 1) + p))
+    rng = np.random.Generator(np.random.PCG64(10_000 * config + p))  # SURVEY.md 8(d)
     if config == 0:
         kind, n_, rho, f0, f1 = 0, 2000, 0.40, 577.0, 577.0
     elif config == 1:
@@ -53,6 +53,8 @@ def make_pair(config, p, n=None, outlier_ratio=None):
     x0, x1, z0, z1 = x0[:n].copy(), x1[:n].copy(), z0[:n], z1[:n]
     x0 += rng.normal(0, 0.5, x0.shape); x1 += rng.normal(0, 0.5, x1.shape)
     al = rng.uniform(0.5, 2.0, 2); of = rng.uniform(-0.2, 0.3, 2)
+    if zero_offsets:  # priors that are off by a scale only (use_shift = False / the scale-only estimator)
+        of = np.zeros(2)
     d0 = (z0 / al[0] - of[0]) * (1 + rng.normal(0, 0.02, n))
     d1 = (z1 / al[1] - of[1]) * (1 + rng.normal(0, 0.02, n))
     n_out = int(round(rho * n))

@@ -214,4 +214,34 @@ inline void kabsch(int n, const double (*X)[3], const double (*Y)[3], double *R,
     for (int k = 0; k < 3; k++) t[k] = cy[k] - Rc[k];
 }
 
+// estimate_scale_and_pose (solver.cpp:5-33): weighted Umeyama.  Centroids and the covariance are weighted, the
+// scale is the UNWEIGHTED ratio sum(Yc . R Xc) / sum(R Xc . R Xc) (solver.cpp:28-29), t = cY - scale R cX.
+inline void umeyama(int n, const double (*X)[3], const double (*Y)[3], const double *W, double *R, double *t, double *scale) {
+    double cx[3] = {0, 0, 0}, cy[3] = {0, 0, 0}, ws = 0;
+    for (int i = 0; i < n; i++) {
+        ws += W[i];
+        for (int k = 0; k < 3; k++) { cx[k] += X[i][k] * W[i]; cy[k] += Y[i][k] * W[i]; }
+    }
+    for (int k = 0; k < 3; k++) { cx[k] /= ws; cy[k] /= ws; }
+    double S[9] = {0};
+    for (int i = 0; i < n; i++)
+        for (int a = 0; a < 3; a++)
+            for (int b = 0; b < 3; b++) S[3 * a + b] += (Y[i][a] - cy[a]) * W[i] * (X[i][b] - cx[b]);
+    double U[9], Sg[3], V[9], Vt[9];
+    jacobi_svd(3, S, U, Sg, V);
+    if (mat3_det(U) * mat3_det(V) < 0) { U[2] = -U[2]; U[5] = -U[5]; U[8] = -U[8]; }
+    mat3_T(V, Vt);
+    mat3_mul(U, Vt, R);
+    double num = 0, den = 0;
+    for (int i = 0; i < n; i++) {
+        double xc[3] = {X[i][0] - cx[0], X[i][1] - cx[1], X[i][2] - cx[2]}, xr[3];
+        mat3_vec(R, xc, xr);
+        for (int k = 0; k < 3; k++) { num += (Y[i][k] - cy[k]) * xr[k]; den += xr[k] * xr[k]; }
+    }
+    *scale = num / den;
+    double Rc[3];
+    mat3_vec(R, cx, Rc);
+    for (int k = 0; k < 3; k++) t[k] = cy[k] - *scale * Rc[k];
+}
+
 } // namespace om

@@ -28,6 +28,7 @@ static_assert(sizeof(Model) == sizeof(mp_model), "model layout");
 
 struct Problem {
     int kind = 0, n = 0;
+    bool scale_only = false;     // HybridEstimatePoseAndScale (hybrid_pose_estimator.cpp:37-63,297-442): calibrated, no offsets
     std::vector<double> x0, x1; // 2n, pixels (calibrated) or pp-subtracted / norm_scale (focal kinds)
     std::vector<double> d0, d1;
     double K0[9], K1[9], K0i[9], K1i[9];
@@ -55,6 +56,8 @@ inline double normalize_points_scale(const std::vector<double> &a, const std::ve
 }
 
 inline void make_problem(int kind, const mp_pair &pr, const mp_options &opt, const mp_config &cfg, Problem *P) {
+    P->scale_only = kind == 3; // MP_KIND_SCALE_ONLY: the calibrated estimator's scale-only twin
+    if (kind == 3) kind = CALIB;
     P->kind = kind; P->n = pr.n; P->opt = opt; P->cfg = cfg;
     int n = pr.n;
     P->x0.assign(pr.x0, pr.x0 + 2 * n); P->x1.assign(pr.x1, pr.x1 + 2 * n);
@@ -145,6 +148,7 @@ inline double evaluate(const Problem &P, const Model &m, int t, int i, bool for_
         for (int k = 0; k < 3; k++) q[k] += m.t[k];
         mat3_vec(K1, q, p);
         if (p[2] < 1e-2) return kMax;
+        if (P.scale_only && P.d0[i] < 1e-2) return kMax; // hybrid_pose_estimator.cpp:386 (quirk Q16)
         double u = p[0] / p[2] - h1[0], v = p[1] / p[2] - h1[1];
         return u * u + v * v;
     } else if (t == 1) {
@@ -157,6 +161,7 @@ inline double evaluate(const Problem &P, const Model &m, int t, int i, bool for_
         for (int k = 0; k < 3; k++) q[k] -= Rt_t[k];
         mat3_vec(K0, q, p);
         if (p[2] < 1e-2) return kMax;
+        if (P.scale_only && P.d1[i] < 1e-2) return kMax; // hybrid_pose_estimator.cpp:398
         double u = p[0] / p[2] - h0[0], v = p[1] / p[2] - h0[1];
         return u * u + v * v;
     } else {

@@ -102,7 +102,17 @@ inline bool cholesky_solve(int n, const double *A, const double *b, double *x) {
 
 // NonMinimalSolver / LeastSquares.  Returns false when the guard rejects the sample
 // (model untouched); true otherwise (like optimizer.h:113-125, whatever Ceres did).
-inline bool lm_solve(const Problem &P, const std::vector<int> *idx, Model *m, LmInfo *info) {
+// nonminimal: the call is NonMinimalSolver (true) or LeastSquares (false).  EstimatorConfig::use_shift reaches the
+// optimiser only at hybrid_pose_estimator.cpp:206,281 (calibrated, both calls) and
+// hybrid_pose_shared_focal_estimator.cpp:149 (shared focal, NonMinimalSolver only); the scale-only optimiser
+// (optimizer.h:133-245) always holds the offsets constant and sets no offset bounds.
+inline bool lm_use_shift(const Problem &P, bool nonminimal) {
+    if (P.scale_only) return false;
+    if (P.kind == CALIB) return P.cfg.use_shift != 0;
+    if (P.kind == SHARED) return nonminimal ? P.cfg.use_shift != 0 : true;
+    return true;
+}
+inline bool lm_solve(const Problem &P, const std::vector<int> *idx, Model *m, LmInfo *info, bool nonminimal = false) {
     LmInfo dummy; if (!info) info = &dummy; *info = LmInfo();
     const int k0 = P.sizes[0][0], k2 = P.sizes[1][2];
     if (((int)idx[0].size() < k0 && (int)idx[1].size() < k0) || (int)idx[2].size() < k2) return false;
@@ -113,14 +123,15 @@ inline bool lm_solve(const Problem &P, const std::vector<int> *idx, Model *m, Lm
     const bool b0 = L.use_reproj && !idx[0].empty(), b1 = L.use_reproj && !idx[1].empty(), b2 = L.use_samp && !idx[2].empty();
     if (!b0 && !b1 && !b2) return false;
     bool act[NT];
-    act[0] = b0 && P.cfg.use_shift; act[1] = act[2] = act[3] = act[4] = act[5] = act[6] = true;
-    act[7] = b1; act[8] = b1 && P.cfg.use_shift; act[9] = P.kind != CALIB; act[10] = P.kind == TWO;
+    const bool shift = lm_use_shift(P, nonminimal);
+    act[0] = b0 && shift; act[1] = act[2] = act[3] = act[4] = act[5] = act[6] = true;
+    act[7] = b1; act[8] = b1 && shift; act[9] = P.kind != CALIB; act[10] = P.kind == TWO;
     L.nt = 0;
     for (int s = 0; s < NT; s++) L.slot[s] = act[s] ? L.nt++ : -1;
     for (int k = 0; k < NA; k++) { L.has_lower[k] = false; L.lower[k] = 0; }
     if (b1) { L.has_lower[8] = true; L.lower[8] = 1e-2; }
-    if (P.cfg.min_depth_constraint && b0) { L.has_lower[0] = true; L.lower[0] = -P.min_depth[0] + 1e-2; }
-    if (P.cfg.min_depth_constraint && b1) { L.has_lower[9] = true; L.lower[9] = -P.min_depth[1] + 1e-2; }
+    if (!P.scale_only && P.cfg.min_depth_constraint && b0) { L.has_lower[0] = true; L.lower[0] = -P.min_depth[0] + 1e-2; }
+    if (!P.scale_only && P.cfg.min_depth_constraint && b1) { L.has_lower[9] = true; L.lower[9] = -P.min_depth[1] + 1e-2; }
     if (P.kind == TWO) { L.has_lower[10] = L.has_lower[11] = true; L.lower[10] = L.lower[11] = 1e-6; }
     double x[NA];
     x[0] = m->o0; rot_to_quat(m->R, x + 1); std::memcpy(x + 5, m->t, 24); x[8] = m->scale; x[9] = m->o1; x[10] = m->f0; x[11] = m->f1;

@@ -2,7 +2,8 @@
 //   /root/reference/src/hybrid_pose_estimator.cpp:65-187
 //   /root/reference/src/hybrid_pose_shared_focal_estimator.cpp:53-130
 //   /root/reference/src/hybrid_pose_two_focal_estimator.cpp:77-185
-// (use_shift = true branches; use_ours / use_4p4d variants are out of scope.)
+// including the use_shift = false branches of the calibrated estimator (:87-120, :146-157) and the
+// scale-only estimator's MinimalSolver (:322-367).
 #pragma once
 #include "om_affine.h"
 #include "om_relpose.h"
@@ -26,6 +27,35 @@ inline void minimal_affine(const Problem &P, const int *idx, std::vector<Model> 
         if (P.kind == CALIB) { mat3_vec(P.K0i, h0, x0[k]); mat3_vec(P.K1i, h1, x1[k]); }
         else { std::memcpy(x0[k], h0, 24); std::memcpy(x1[k], h1, 24); }
         d0[k] = P.d0[i]; d1[k] = P.d1[i];
+    }
+    if (P.scale_only) { // hybrid_pose_estimator.cpp:325-331: Umeyama on the homogeneous rays (no depths), unit weights
+        Model m;
+        const double w[3] = {1, 1, 1};
+        double sc;
+        umeyama(3, x0, x1, w, m.R, m.t, &sc);
+        m.scale = 1.0 / sc; // "scale now applies on the second camera"
+        if (model_finite(m)) models->push_back(m);
+        return;
+    }
+    if (P.kind == CALIB && !P.cfg.use_shift) { // hybrid_pose_estimator.cpp:87-120
+        double p0[3][3], p1[3][3];
+        for (int k = 0; k < 3; k++)
+            for (int c = 0; c < 3; c++) { p0[k][c] = x0[k][c] * d0[k]; p1[k][c] = x1[k][c] * d1[k]; }
+        auto dist = [](const double *a, const double *b) {
+            double e[3] = {a[0] - b[0], a[1] - b[1], a[2] - b[2]};
+            return norm3(e);
+        };
+        const double v0[3] = {dist(p0[0], p0[1]), dist(p0[0], p0[2]), dist(p0[1], p0[2])};
+        const double v1[3] = {dist(p1[0], p1[1]), dist(p1[0], p1[2]), dist(p1[1], p1[2])};
+        const double scale = dot3(v1, v0) / dot3(v1, v1); // least-squares s with s * v1 = v0
+        double Y[3][3];
+        for (int k = 0; k < 3; k++)
+            for (int c = 0; c < 3; c++) Y[k][c] = x1[k][c] * (d1[k] * scale);
+        Model m;
+        kabsch(3, p0, Y, m.R, m.t);
+        m.scale = scale;
+        if (model_finite(m)) models->push_back(m);
+        return;
     }
     std::vector<AffineSol> sols;
     if (P.kind == CALIB) {
@@ -67,6 +97,22 @@ inline bool depth_fit_tail(const Problem &P, int np, const int *idx, const doubl
     }
     double X[7][3], z[7], d[7];
     for (int k = 0; k < np; k++) { triangulate(P0, P1, p0[k], p1[k], X[k]); z[k] = X[k][2]; d[k] = P.d0[idx[k]]; }
+    if (P.scale_only || (P.kind == CALIB && !P.cfg.use_shift)) { // scale-only fits, no filter (:146-157, :351-363)
+        auto ratio = [&](const double *dd, const double *zz) {
+            double num = 0, den = 0;
+            for (int k = 0; k < np; k++) { num += dd[k] * zz[k]; den += dd[k] * dd[k]; }
+            return num / den;
+        };
+        const double s0 = ratio(d, z);
+        for (int k = 0; k < 3; k++) m->t[k] /= s0;
+        for (int k = 0; k < np; k++) {
+            double Xs[3] = {X[k][0] / s0, X[k][1] / s0, X[k][2] / s0}, Y[3];
+            mat3_vec(m->R, Xs, Y);
+            z[k] = Y[2] + m->t[2]; d[k] = P.d1[idx[k]];
+        }
+        m->scale = ratio(d, z); m->o0 = 0; m->o1 = 0;
+        return model_finite(*m);
+    }
     double s0, c0;
     fit_affine(np, d, z, &s0, &c0);
     double off0 = c0 / s0;

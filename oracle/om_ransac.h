@@ -26,7 +26,9 @@ struct Stats {
     uint32_t lm_solves = 0, lm_iterations = 0;
 };
 
-// one record per main-loop iteration, for debugging parity: {it, solver, n_models, best_local_score}
+// chronological records of 4 doubles, for parity forensics (tests/test_estimate_gpu.py::explain_fork):
+//   {it, solver, n_models, best_local_score}   one per main-loop iteration
+//   {it, -1, 0, score}                         every ScoreModel inside LocalOptimization / the final least squares
 typedef std::vector<double> Trace;
 
 struct Ransac {
@@ -39,9 +41,11 @@ struct Ransac {
 
     Ransac(const Problem &p, Stats &s, Trace *t) : P(p), st(s), trace(t) {}
 
-    double score(const Model &m) {
+    double score(const Model &m, bool lo_event = false) {
         st.hypotheses_scored++; st.residual_evals += P.n;
-        return score_model(P, m);
+        const double sc = score_model(P, m);
+        if (trace && lo_event) { trace->push_back(st.num_iterations_total); trace->push_back(-1); trace->push_back(0); trace->push_back(sc); }
+        return sc;
     }
     void lsq(const std::vector<std::vector<int>> &sample, Model *m) {
         LmInfo info;
@@ -112,7 +116,7 @@ struct Ransac {
         }
         Model m_init = *best;
         least_squares_fit(thr, solver, &m_init, true);
-        double sc = score(m_init);
+        double sc = score(m_init, true);
         update_best(sc, m_init, solver, best_score, best, best_solver);
         std::vector<std::vector<int>> base;
         get_inliers(P, m_init, P.thr, &base);
@@ -127,15 +131,15 @@ struct Ransac {
             unflatten(cur, &sample);
             Model m = m_init;
             LmInfo info;
-            if (!lm_solve(P, sample.data(), &m, &info)) continue;
+            if (!lm_solve(P, sample.data(), &m, &info, true)) continue;
             st.lm_solves++; st.lm_iterations += info.iterations;
-            sc = score(m);
+            sc = score(m, true);
             update_best(sc, m, solver, best_score, best, best_solver);
             least_squares_fit(P.thr, solver, &m, false);
             double cur_thr[3] = {thr[0], thr[1], thr[2]};
             for (int i = 0; i < P.opt.num_lsq_iterations; ++i) {
                 least_squares_fit(cur_thr, solver, &m, false);
-                sc = score(m);
+                sc = score(m, true);
                 update_best(sc, m, solver, best_score, best, best_solver);
                 for (int t = 0; t < 3; t++) cur_thr[t] -= step[t];
             }
@@ -244,7 +248,7 @@ struct Ransac {
         if (P.opt.final_least_squares) {
             Model refined = *best_model;
             lsq(st.inlier_indices, &refined);
-            double sc = score(refined);
+            double sc = score(refined, true);
             if (sc < st.best_model_score) { st.best_model_score = sc; *best_model = refined; update_termination(*best_model); }
         }
         return st.best_num_inliers;

@@ -90,7 +90,7 @@ int om_minimal_solve(int kind, const mp_pair *pair, const mp_options *opt, const
 
 // NonMinimalSolver / LeastSquares: problem j uses idx[off[3j+t] .. off[3j+t+1]) for type t
 int om_lm(int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, int n_problems,
-          const mp_model *start, const int *idx, const int *off, mp_model *out_models, double *out_info) {
+          const mp_model *start, const int *idx, const int *off, mp_model *out_models, double *out_info, int nonminimal) {
     om::Problem P;
     om::make_problem(kind, *pair, *opt, *cfg, &P);
     for (int j = 0; j < n_problems; j++) {
@@ -98,7 +98,7 @@ int om_lm(int kind, const mp_pair *pair, const mp_options *opt, const mp_config 
         for (int t = 0; t < 3; t++) s[t].assign(idx + off[3 * j + t], idx + off[3 * j + t + 1]);
         om::Model m = *reinterpret_cast<const om::Model *>(start + j);
         om::LmInfo info;
-        om::lm_solve(P, s, &m, &info);
+        om::lm_solve(P, s, &m, &info, nonminimal != 0);
         std::memcpy(out_models + j, &m, sizeof(mp_model));
         out_info[4 * j] = info.iterations; out_info[4 * j + 1] = info.termination;
         out_info[4 * j + 2] = info.cost0; out_info[4 * j + 3] = info.cost;
@@ -139,7 +139,7 @@ static void fill_stats(const om::Stats &st, int n, mp_stats *o, int *inl) {
 }
 
 // whole path for a batch of pairs on `threads` host threads (pair p -> thread p % threads).
-// out_inliers layout = mp_estimate_batch.  trace (optional, pair 0 only): up to trace_cap doubles.
+// out_inliers layout = mp_estimate_batch.  trace (optional, pair 0 only): up to trace_cap doubles, -1 terminated.
 int om_estimate_batch(int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt, const mp_config *cfg,
                       mp_model *out_models, mp_stats *out_stats, int *out_inliers, int threads, double *trace,
                       int trace_cap) {

@@ -41,7 +41,7 @@ struct Adapter {
     }
     int NonMinimalSolver(const std::vector<std::vector<int>> &sample, const int, om::Model *m) const {
         om::LmInfo info;
-        if (!om::lm_solve(P, sample.data(), m, &info)) return 0;
+        if (!om::lm_solve(P, sample.data(), m, &info, true)) return 0;
         st->lm_solves++; st->lm_iterations += info.iterations;
         return 1;
     }

@@ -3,6 +3,8 @@ import sys
 
 import pytest
 
+# caller-side setting of the library's stream count: before the process creates its CUDA context
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -4,12 +4,12 @@ import numpy as np
 from madpose_b200 import capi, synth
 
 
-def problem(config, p=0, n=None, **optkw):
-    d = synth.make_pair(config, p, n=n)
+def problem(config, p=0, n=None, zero_offsets=False, cfg=None, **optkw):
+    d = synth.make_pair(config, p, n=n, zero_offsets=zero_offsets)
     o = synth.options_for(config)
     o.update(optkw)
     opt = capi.Options(**o)
-    cfg = capi.Config()
+    cfg = capi.Config(**(cfg or {}))
     pair, keep = capi.make_pair(d["x0"], d["x1"], d["d0"], d["d1"], d["min_depth"], d["K0"], d["K1"], d["pp0"], d["pp1"])
     return d, pair, opt, cfg, keep
 

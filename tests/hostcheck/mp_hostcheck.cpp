@@ -20,6 +20,8 @@ struct HostPair {
 void build(int kind, const mp_pair *pr, const mp_options *opt, HostPair *hp) {
     PairRaw r;
     std::memset(&r, 0, sizeof(r));
+    r.scale_only = kind == 3 ? 1 : 0;
+    if (kind == 3) kind = CALIB;
     r.n = pr->n; r.kind = kind; r.off = 0; r.off32 = 0;
     std::memcpy(r.K0, pr->K0, 72); std::memcpy(r.K1, pr->K1, 72);
     for (int k = 0; k < 2; k++) {
@@ -47,10 +49,11 @@ int hc_minimal_solve(int kind, const mp_pair *pair, const mp_options *opt, const
                      int n_samples, const int *idx, int max_models, mp_model *out_models, int *out_counts) {
     HostPair hp;
     build(kind, pair, opt, &hp);
+    if (kind == 3) kind = CALIB;
     const int k = solver_idx == 0 ? (kind == CALIB ? 3 : 4) : (kind == CALIB ? 5 : (kind == SHARED ? 6 : 7));
     Model tmp[kMaxModelsAny];
     for (int s = 0; s < n_samples; s++) {
-        int c = minimal_solver(hp.pc, hp.M.data(), solver_idx, idx + (size_t)s * k, cfg->min_depth_constraint != 0, tmp);
+        int c = minimal_solver(hp.pc, hp.M.data(), solver_idx, idx + (size_t)s * k, minimal_flags(*cfg), tmp);
         if (c > max_models) c = max_models;
         out_counts[s] = c;
         for (int j = 0; j < c; j++) std::memcpy(out_models + (size_t)s * max_models + j, &tmp[j], sizeof(mp_model));

@@ -27,7 +27,7 @@ class HostCheck:
         return [out[i, :cnt[i]].copy() for i in range(ns)]
 
 
-    def lm(self, kind, pair, opt, cfg, starts, samples):
+    def lm(self, kind, pair, opt, cfg, starts, samples, nonminimal=False):
         st = np.ascontiguousarray(starts, np.float64).reshape(-1, 17)
         flat, off = [], [0]
         for s3 in samples:
@@ -36,7 +36,7 @@ class HostCheck:
         idx = np.array(flat + [0], np.int32); off = np.array(off, np.int32)
         out = np.zeros_like(st); info = np.zeros((st.shape[0], 4))
         self.lib.hc_lm(kind, C.byref(pair), C.byref(opt), C.byref(cfg), st.shape[0], _ptr(st), _ptr(idx), _ptr(off),
-                       _ptr(out), _ptr(info))
+                       _ptr(out), _ptr(info), int(nonminimal))
         return out, info
 
 

@@ -54,7 +54,7 @@ class Oracle:
                                   max_models, _ptr(out), _ptr(cnt))
         return [out[i, :cnt[i]].copy() for i in range(ns)]
 
-    def lm(self, kind, pair, opt, cfg, starts, samples):
+    def lm(self, kind, pair, opt, cfg, starts, samples, nonminimal=False):
         """samples: list (per problem) of 3 index arrays."""
         st = np.ascontiguousarray(starts, np.float64).reshape(-1, 17)
         flat, off = [], [0]
@@ -64,7 +64,7 @@ class Oracle:
         idx = np.array(flat + [0], np.int32); off = np.array(off, np.int32)
         out = np.zeros_like(st); info = np.zeros((st.shape[0], 4))
         self.lib.om_lm(kind, C.byref(pair), C.byref(opt), C.byref(cfg), st.shape[0], _ptr(st), _ptr(idx), _ptr(off),
-                       _ptr(out), _ptr(info))
+                       _ptr(out), _ptr(info), int(nonminimal))
         return out, info
 
     def estimate_batch(self, kind, pairs, opt, cfg, threads=1, trace_cap=0, lib=None):

@@ -41,8 +41,13 @@ def test_api_surface_matches_reference():
                  "HybridEstimatePoseScaleOffsetSharedFocal", "HybridEstimatePoseScaleOffsetTwoFocal",
                  "HybridEstimatePoseAndScale", "solve_scale_and_shift", "solve_scale_shift_pose_two_focal"):
         assert hasattr(madpose, name)
-    with pytest.raises(NotImplementedError):
-        madpose.solve_scale_and_shift(np.eye(3), np.eye(3), np.ones(3), np.ones(3))
+    for name in ("estimate_scale_and_pose", "solve_scale_and_shift_shared_focal", "solve_scale_and_shift_two_focal",
+                 "solve_scale_shift_pose", "solve_scale_shift_pose_shared_focal", "PoseAndScale"):
+        assert hasattr(madpose, name)      # bindings.cpp:111-118,156-166
+    ps = madpose.PoseAndScale(np.eye(3), np.array([1., 2, 3]), 2.5)
+    assert ps.scale == 2.5 and np.allclose(ps.t(), [1, 2, 3]) and ps.pose.shape == (3, 4) and madpose.PoseAndScale().scale == 1
+    with pytest.raises(ValueError, match="3x3"):   # argument validation happens before any device call
+        madpose.solve_scale_and_shift(np.eye(4), np.eye(3), np.ones(3), np.ones(3))
 
 
 def test_argument_validation():
@@ -103,3 +108,63 @@ def test_batch_superset_call():
         assert stats.num_iterations_total == s1.num_iterations_total
         R = pose.R()
         assert np.degrees(np.arccos(np.clip((np.trace(R.T @ d["gt"]["R"]) - 1) / 2, -1, 1))) < 3.0
+
+
+@pytest.mark.gpu
+def test_solver_functions_match_reference_numpy_goldens():
+    """solve_scale_and_shift{,_shared_focal,_two_focal} and solve_scale_shift_pose* (bindings.cpp:157-166) on the GPU
+    against the outputs of the reference's own numpy solvers (tests/golden/affine_solvers.json): solution sets to 1e-7,
+    and every returned pose maps the corrected back-projections of view 0 onto those of view 1."""
+    import json
+    import os
+    cases = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "affine_solvers.json")))
+    raw = [madpose.solve_scale_and_shift, madpose.solve_scale_and_shift_shared_focal, madpose.solve_scale_and_shift_two_focal]
+    pose = [madpose.solve_scale_shift_pose, madpose.solve_scale_shift_pose_shared_focal, madpose.solve_scale_shift_pose_two_focal]
+    n_ref = n_pose = 0
+    for g in cases:
+        k = g["kind"]
+        xh, yh = np.array(g["x1"]).T.copy(), np.array(g["x2"]).T.copy()   # 3 x NP, columns = homogeneous points
+        d1, d2 = np.array(g["d1"]), np.array(g["d2"])
+        mine = np.array(raw[k](xh, yh, d1, d2)).reshape(-1, 4 + k)
+        ref = np.array(g["sols"]).reshape(-1, 4 + k)
+        assert len(mine) == len(ref)
+        for r in ref:
+            n_ref += 1
+            err = np.max(np.abs(mine[:, 1:] - r[1:]) / np.maximum(np.abs(r[1:]), 1e-300), axis=1)
+            assert err.min() < 1e-7 and np.all(mine[:, 0] == 1.0)
+        for m in pose[k](xh, yh, d1, d2):
+            n_pose += 1
+            f0 = 1.0 if k == 0 else (m.focal if k == 1 else m.focal0)
+            f1 = 1.0 if k == 0 else (m.focal if k == 1 else m.focal1)
+            X = (xh / np.array([f0, f0, 1.0])[:, None]) * (d1 + m.offset0)
+            Y = (yh / np.array([f1, f1, 1.0])[:, None]) * (d2 * m.scale + m.offset1)
+            assert np.all(d1 + m.offset0 > 0) and np.all(d2 * m.scale + m.offset1 > 0)   # solver.cpp:503,702,1006
+            res = m.R() @ X + m.t()[:, None] - Y
+            assert np.max(np.abs(res)) <= 1e-6 * max(1.0, np.max(np.abs(Y))), "pose does not align the corrected points"
+            assert abs(np.linalg.det(m.R()) - 1) < 1e-9
+    assert n_ref > 250 and n_pose > 100
+
+
+@pytest.mark.gpu
+def test_estimate_scale_and_pose_and_scale_only_estimator(oracle):
+    """estimate_scale_and_pose (solver.cpp:5-33) on a synthetic similarity; HybridEstimatePoseAndScale
+    (hybrid_pose_estimator.cpp:37-63) against the oracle's scale-only path."""
+    from madpose_b200 import capi
+    from tests.helpers import problem
+    rng = np.random.default_rng(3)
+    X = rng.standard_normal((3, 12))
+    R = np.linalg.qr(rng.standard_normal((3, 3)))[0]; R *= np.linalg.det(R)
+    t, sc = rng.standard_normal(3), 1.7
+    Y = sc * R @ X + t[:, None]
+    ps = madpose.estimate_scale_and_pose(X, Y, rng.uniform(0.5, 2.0, 12))
+    np.testing.assert_allclose(ps.R(), R, atol=1e-10); np.testing.assert_allclose(ps.t(), t, atol=1e-10)
+    assert abs(ps.scale - sc) < 1e-10
+    d, pair, opt, cfg, keep = problem(0, p=9, zero_offsets=True)
+    pose, stats = madpose.HybridEstimatePoseAndScale(d["x0"], d["x1"], d["d0"], d["d1"], d["K0"], d["K1"], _options(0))
+    mo, so, io = oracle.estimate_batch(capi.KIND_SCALE_ONLY, [pair], opt, cfg)
+    assert stats.num_iterations_total == so[0].num_iterations_total and stats.best_num_inliers == so[0].best_num_inliers
+    np.testing.assert_allclose(pose.R().reshape(9), mo[0][:9], atol=1e-9)
+    np.testing.assert_allclose(pose.t(), mo[0][9:12], rtol=1e-6, atol=1e-9)
+    assert abs(pose.scale / mo[0][12] - 1) < 1e-6
+    Rg = d["gt"]["R"]
+    assert np.degrees(np.arccos(np.clip((np.trace(pose.R().T @ Rg) - 1) / 2, -1, 1))) < 2.0
