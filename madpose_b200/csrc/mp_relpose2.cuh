@@ -70,6 +70,24 @@ MP_HD void det10_complex(const double (*Cw)[100], double wr, double wi, double *
 
 struct FocalPose { Pose pose; double focal; };
 
+// Is E an essential matrix?  || 2 E E^T E - tr(E E^T) E ||_F <= tol on the unit-norm matrix.  The hidden-variable
+// determinant has real roots that are not solutions of the ten equations (the polish then stops at a least-squares
+// point with a residual); an exact solver (PoseLib's action matrix) never returns those, so they are dropped.
+MP_HD bool essential_valid(const double *Ein, double tol) {
+    double n = 0, E[9], EEt[9], T[9];
+    for (int k = 0; k < 9; k++) n += Ein[k] * Ein[k];
+    n = sqrt(n);
+    if (!(n > 0) || !finite_d(n)) return false;
+    for (int k = 0; k < 9; k++) E[k] = Ein[k] / n;
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) EEt[3 * i + j] = E[3 * i] * E[3 * j] + E[3 * i + 1] * E[3 * j + 1] + E[3 * i + 2] * E[3 * j + 2];
+    const double tr = EEt[0] + EEt[4] + EEt[8];
+    mat3_mul(EEt, E, T);
+    double r = 0;
+    for (int k = 0; k < 9; k++) { const double v = 2 * T[k] - tr * E[k]; r += v * v; }
+    return sqrt(r) <= tol;
+}
+
 // x1, x2: 6 points (x, y, 1) in (normalised) pixel units, one shared unknown focal.  <= 15 candidates
 MP_HD int relpose_6pt_shared_focal(const double (*x1)[3], const double (*x2)[3], FocalPose *out) {
     double A[54], N[27];
@@ -213,6 +231,7 @@ MP_HD int relpose_6pt_shared_focal(const double (*x1)[3], const double (*x2)[3],
         for (int i = 0; i < 3; i++)
             for (int j = 0; j < 3; j++)
                 E[3 * i + j] = (a * N[3 * i + j] + b * N[9 + 3 * i + j] + N[18 + 3 * i + j]) * (i < 2 ? f : 1.0) * (j < 2 ? f : 1.0);
+        if (!essential_valid(E, 1e-8)) continue;
         double b1[6][3], b2[6][3];
         for (int i = 0; i < 6; i++) {
             const double p[3] = {x1[i][0] / f, x1[i][1] / f, 1.0}, qv[3] = {x2[i][0] / f, x2[i][1] / f, 1.0};

@@ -106,6 +106,73 @@ int om_lm(int kind, const mp_pair *pair, const mp_options *opt, const mp_config 
     return 0;
 }
 
+// ---- direct access to the restated third-party solvers (cross-checked against OpenCV / constraint identities /
+// scipy in tests/test_oracle_pins.py).  x0, x1: n x 3 row-major.
+// 5-point: unit bearings -> essential matrices (row-major 9 each, up to 10) and the poses relpose_5pt keeps
+int om_relpose_5pt(const double *x0, const double *x1, double *Es, int *nE, double *poses12, int *nP) {
+    double a[5][3], b[5][3];
+    std::memcpy(a, x0, sizeof(a)); std::memcpy(b, x1, sizeof(b));
+    std::vector<std::vector<double>> E;
+    om::relpose_5pt_essential(a, b, &E);
+    *nE = (int)E.size();
+    for (size_t i = 0; i < E.size(); i++) std::memcpy(Es + 9 * i, E[i].data(), 72);
+    std::vector<om::Pose> P;
+    om::relpose_5pt(a, b, &P);
+    *nP = (int)P.size();
+    for (size_t i = 0; i < P.size(); i++) { std::memcpy(poses12 + 12 * i, P[i].R, 72); std::memcpy(poses12 + 12 * i + 9, P[i].t, 24); }
+    return 0;
+}
+// 7-point: homogeneous points -> fundamental matrices (up to 3)
+int om_relpose_7pt(const double *x0, const double *x1, double *Fs, int *nF) {
+    double a[7][3], b[7][3];
+    std::memcpy(a, x0, sizeof(a)); std::memcpy(b, x1, sizeof(b));
+    std::vector<std::vector<double>> F;
+    om::relpose_7pt(a, b, &F);
+    *nF = (int)F.size();
+    for (size_t i = 0; i < F.size(); i++) std::memcpy(Fs + 9 * i, F[i].data(), 72);
+    return 0;
+}
+// 6-point shared focal: (x, y, 1) points -> (R, t, f) candidates (13 doubles each, up to 15)
+int om_relpose_6pt_focal(const double *x0, const double *x1, double *out13, int *n) {
+    double a[6][3], b[6][3];
+    std::memcpy(a, x0, sizeof(a)); std::memcpy(b, x1, sizeof(b));
+    std::vector<om::FocalPose> fp;
+    om::relpose_6pt_shared_focal(a, b, &fp);
+    *n = (int)fp.size();
+    for (size_t i = 0; i < fp.size(); i++) {
+        std::memcpy(out13 + 13 * i, fp[i].pose.R, 72); std::memcpy(out13 + 13 * i + 9, fp[i].pose.t, 24); out13[13 * i + 12] = fp[i].focal;
+    }
+    return 0;
+}
+// cv::recoverPose restatement: p0, p1 n x 2
+int om_recover_pose(const double *E, int n, const double *p0, const double *p1, double dist, double *R, double *t) {
+    om::recover_pose(E, n, reinterpret_cast<const double (*)[2]>(p0), reinterpret_cast<const double (*)[2]>(p1), dist, R, t);
+    return 0;
+}
+int om_bougnoux(const double *F, double *f0sq, double *f1sq) { om::bougnoux_focals(F, f0sq, f1sq); return 0; }
+// residual vector of the LM problem at a model (the functors of cost_functions.h in the order of optimizer.h:54-77)
+// out: 2 n0 + 2 n1 + n2 doubles; returns the count
+int om_lm_residuals(int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg, const mp_model *model,
+                    const int *idx, const int *off, double *out) {
+    om::Problem P;
+    om::make_problem(kind, *pair, *opt, *cfg, &P);
+    const om::Model &m = *reinterpret_cast<const om::Model *>(model);
+    om::LmData D; D.P = &P;
+    const double sw = std::sqrt(P.sampson_w);
+    D.W = P.kind == om::CALIB ? sw / (1.0 / (P.K0[0] + P.K0[4]) + 1.0 / (P.K1[0] + P.K1[4])) : sw;
+    double x[om::NA];
+    x[0] = m.o0; om::rot_to_quat(m.R, x + 1); std::memcpy(x + 5, m.t, 24); x[8] = m.scale; x[9] = m.o1; x[10] = m.f0; x[11] = m.f1;
+    double f0 = x[10], f1 = P.kind == om::TWO ? x[11] : x[10];
+    int k = 0;
+    double r[2];
+    if (P.cfg.lo_type != 1) {
+        for (int j = off[0]; j < off[1]; j++) { om::res_reproj0<double>(D, idx[j], x, f0, f1, r); out[k++] = r[0]; out[k++] = r[1]; }
+        for (int j = off[1]; j < off[2]; j++) { om::res_reproj1<double>(D, idx[j], x, f0, f1, r); out[k++] = r[0]; out[k++] = r[1]; }
+    }
+    if (P.cfg.lo_type != 2) for (int j = off[2]; j < off[3]; j++) { om::res_sampson<double>(D, idx[j], x, f0, f1, r); out[k++] = r[0]; }
+    return k;
+}
+
 // utils::NumRequiredIterations restatement (KAT-1b of SURVEY.md Appendix C)
 unsigned om_num_required_iterations(const double *ratios3, double prob_missing, const int *sizes3, unsigned mn, unsigned mx) {
     return om::Ransac::num_required_iterations(ratios3, prob_missing, sizes3, mn, mx);
