@@ -99,6 +99,8 @@ typedef struct mp_stats {
     uint32_t lm_solves, lm_iterations;
     uint64_t evals_fp64;     /* exact fp64 (model x match) evaluations: re-scoring, GetInliers, LO scoring */
     uint64_t lm_block_evals; /* residual blocks evaluated (with Jacobian) over all LM iterations */
+    uint64_t evals_fp32;     /* (model x match) evaluations the fused fp32 scoring kernel performed for this pair, including
+                              * the speculated iterations that were discarded after a local optimisation */
 } mp_stats;
 
 typedef struct mp_ctx mp_ctx;

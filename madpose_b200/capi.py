@@ -87,7 +87,7 @@ class Stats(C.Structure):
         ("best_model_score", C.c_double), ("inlier_ratios", C.c_double * 3),
         ("hypotheses_scored", C.c_uint64), ("residual_evals", C.c_uint64),
         ("lm_solves", C.c_uint32), ("lm_iterations", C.c_uint32),
-        ("evals_fp64", C.c_uint64), ("lm_block_evals", C.c_uint64),
+        ("evals_fp64", C.c_uint64), ("lm_block_evals", C.c_uint64), ("evals_fp32", C.c_uint64),
     ]
 
 

@@ -30,7 +30,7 @@ __global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp
     o.reserved_ = 0;
     o.best_model_score = S.best_score;
     o.hypotheses_scored = S.hyps_scored; o.residual_evals = S.evals; o.lm_solves = S.lm_solves; o.lm_iterations = S.lm_iters;
-    o.evals_fp64 = S.evals64; o.lm_block_evals = S.lm_blocks;
+    o.evals_fp64 = S.evals64; o.lm_block_evals = S.lm_blocks; o.evals_fp32 = L.evals32[p];
     stats[p] = o;
 }
 
@@ -153,6 +153,8 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.items = A.items.as<int>(); L.n_pairs = n_pairs;
     L.lo_req = A.lo_req.as<int>();
     L.gsz = gsz;
+    MP_CUDA(A.evals32.reserve(n_pairs * sizeof(unsigned long long)));
+    L.evals32 = A.evals32.as<unsigned long long>();
     L.trace = nullptr; L.trace_cap = c->trace_cap;
     if (c->trace_cap > 0) {
         MP_CUDA(A.trace.reserve((size_t)n_pairs * c->trace_cap * 2 * sizeof(double)));

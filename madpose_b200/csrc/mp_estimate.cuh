@@ -19,7 +19,7 @@ cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopPara
                            const int *idx, const int *off, Model *out, double *info, bool nonminimal, cudaStream_t s);
 
 struct LoopAlloc {
-    DevBuf trace, st, wk, rngA, rngB, models, hyps, inl_best, inl_cur, flat, sample, misc, off3, caps, prm, out_models, out_stats, lo_req, items, cand, cand_ok;
+    DevBuf trace, evals32, st, wk, rngA, rngB, models, hyps, inl_best, inl_cur, flat, sample, misc, off3, caps, prm, out_models, out_stats, lo_req, items, cand, cand_ok;
     PinBuf h_off3, h_caps, h_prm, h_active, h_out;
 };
 

@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(MP_CTA, 1) score_batch_kernel(LoopBuffers L, c
     __syncthreads();
     const int nh = nlist;
     if (nh == 0) return;
+    if (threadIdx.x == 0) L.evals32[p] += (unsigned long long)nh * (unsigned long long)pc.n;
     const PairF pf = make_pairf(pc, prm.cfg.score_type);
     const float w0 = (float)pc.w[0], w2 = (float)pc.w[2];
     float4 *sP = reinterpret_cast<float4 *>(smem_raw), *sQ = sP + tile_cap;
@@ -62,6 +63,7 @@ template <int KIND> __device__ void block_update_termination(const BlockCtx &C, 
         const int n = C.pc->n;
         S->evals64 += n;
         S->best_num_inliers = sh->cnt[0] + sh->cnt[1] + sh->cnt[2];
+        trace_event(C, -2.0, (double)sh->cnt[0] + 131072.0 * (double)sh->cnt[1] + 17179869184.0 * (double)sh->cnt[2]);
         for (int t = 0; t < 3; t++) { S->num_inl[t] = sh->cnt[t]; S->ratios[t] = n > 0 ? (double)sh->cnt[t] / n : 0.0; }
         for (int s = 0; s < 2; s++)
             S->cap[s] = num_required_iterations(S->ratios, 1.0 - C.prm->opt.success_probability, S->sizes[s],

@@ -98,8 +98,11 @@ struct LoopBuffers {
     // parity forensics (mp_set_trace): per pair trace_cap records of 2 doubles, chronological:
     //   {it, score}   an iteration whose best candidate was re-scored in fp64 (score = the local best)
     //   {-1, score}   every ScoreModel inside LocalOptimization / the final least squares
+    //   {-2, count}   every GetInliers (LeastSquaresFit, LO base, termination update): total inlier count
+    //   {-3, iterations}, {-4, final cost}   every NonMinimalSolver / LeastSquares that ran
     double *trace;
     int trace_cap;
+    unsigned long long *evals32; // per pair: (model x match) evaluations of the fused fp32 scoring kernel
 };
 
 // ---------------------------------------------------------------- block-level helpers

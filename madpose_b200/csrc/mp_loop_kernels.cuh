@@ -39,6 +39,7 @@ __global__ void init_state_kernel(LoopBuffers L, const LoopParams *prmp) {
     S.hyps_scored = 0; S.evals = 0; S.evals64 = 0; S.lm_blocks = 0; S.lm_solves = 0; S.lm_iters = 0;
     for (int q = 0; q < 16; q++) S.clk[q] = 0;
     S.trace_n = 0; S.trace_pad_ = 0;
+    L.evals32[p] = 0;
     mt_seed(&L.rngA[p], prm.opt.random_seed);
     mt_seed(&L.rngB[p], prm.opt.random_seed);
     L.lo_req[p] = 0; L.wk[p].blen = 0;

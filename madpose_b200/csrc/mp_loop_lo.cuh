@@ -164,7 +164,10 @@ template <int KIND> __device__ void block_lsq(const BlockCtx &C, const int *l0, 
     ev.C = &C; ev.L = &sh->lm_setup; ev.lst[0] = l0; ev.lst[1] = l1; ev.lst[2] = l2; ev.n[0] = n0; ev.n[1] = n1; ev.n[2] = n2;
     __shared__ LmInfo info;
     block_lm<KIND>(C, sh->lm_setup, ev, *m, m, &info);
-    if (threadIdx.x == 0) { C.S->lm_solves += 1; C.S->lm_iters += info.iterations; }
+    if (threadIdx.x == 0) {
+        C.S->lm_solves += 1; C.S->lm_iters += info.iterations;
+        trace_event(C, -3.0, (double)info.iterations); trace_event(C, -4.0, info.cost);
+    }
     __syncthreads();
 }
 
@@ -338,7 +341,7 @@ template <int KIND> __device__ __noinline__ void block_lsq_fit(const BlockCtx &C
     BlockScratch *sh = C.sh;
     const int n = C.pc->n;
     if (!have_inliers) { MP_CLK_BEGIN(); block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
-    if (threadIdx.x == 0) C.S->evals64 += n;
+    if (threadIdx.x == 0) { C.S->evals64 += n; trace_event(C, -2.0, (double)sh->cnt[0] + 131072.0 * (double)sh->cnt[1] + 17179869184.0 * (double)sh->cnt[2]); }
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     const int *sz = C.S->sizes[solver];
     if (c0 < sz[0] || c1 < sz[1] || c2 < sz[2]) return;
@@ -406,7 +409,7 @@ template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, 
     // score of m_init + its base inliers at the nominal thresholds (flattened below with type offsets)
     double sc = block_score_inliers(C, sh->m_init, pc.thr);
     update_best(sc, &sh->m_init);
-    if (threadIdx.x == 0) C.S->evals64 += n;
+    if (threadIdx.x == 0) { C.S->evals64 += n; trace_event(C, -2.0, (double)sh->cnt[0] + 131072.0 * (double)sh->cnt[1] + 17179869184.0 * (double)sh->cnt[2]); }
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
     for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
     for (int k = threadIdx.x; k < c1; k += blockDim.x) C.base[c0 + k] = C.inl_cur[n + k] + n;

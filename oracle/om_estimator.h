@@ -192,14 +192,22 @@ inline double score_model(const Problem &P, const Model &m) {
 }
 
 // GetInliers, hybrid_ransac.h:289-349 (common = false, all types)
-inline int get_inliers(const Problem &P, const Model &m, const double *thr, std::vector<std::vector<int>> *inl) {
+// min_rel (optional, parity forensics): the smallest |r^2 - thr_t| / thr_t over all residuals of the pass, i.e. how
+// close the pass came to a tie on the inlier test
+inline int get_inliers(const Problem &P, const Model &m, const double *thr, std::vector<std::vector<int>> *inl,
+                       double *min_rel = nullptr) {
     int cnt = 0;
     inl->resize(3);
+    double mr = kMax;
     for (int t = 0; t < 3; t++) {
         (*inl)[t].clear();
-        for (int i = 0; i < P.n; i++)
-            if (evaluate(P, m, t, i, true) < thr[t]) { cnt++; (*inl)[t].push_back(i); }
+        for (int i = 0; i < P.n; i++) {
+            const double r = evaluate(P, m, t, i, true);
+            if (r < thr[t]) { cnt++; (*inl)[t].push_back(i); }
+            if (min_rel && r < kMax) mr = std::min(mr, std::fabs(r - thr[t]) / thr[t]);
+        }
     }
+    if (min_rel) *min_rel = mr;
     return cnt;
 }
 

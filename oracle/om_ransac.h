@@ -29,6 +29,8 @@ struct Stats {
 // chronological records of 4 doubles, for parity forensics (tests/test_estimate_gpu.py::explain_fork):
 //   {it, solver, n_models, best_local_score}   one per main-loop iteration
 //   {it, -1, 0, score}                         every ScoreModel inside LocalOptimization / the final least squares
+//   {it, -2, inlier count, min |r^2 - thr| / thr}   every GetInliers (LeastSquaresFit, LO base, termination update)
+//   {it, -3, LM iterations, final cost}        every NonMinimalSolver / LeastSquares that ran
 typedef std::vector<double> Trace;
 
 struct Ransac {
@@ -47,9 +49,19 @@ struct Ransac {
         if (trace && lo_event) { trace->push_back(st.num_iterations_total); trace->push_back(-1); trace->push_back(0); trace->push_back(sc); }
         return sc;
     }
+    void trace4(double kind, double a, double b) {
+        if (trace) { trace->push_back(st.num_iterations_total); trace->push_back(kind); trace->push_back(a); trace->push_back(b); }
+    }
+    int inliers_traced(const Model &m, const double *thr, std::vector<std::vector<int>> *inl) {
+        double mr = 0;
+        const int c = get_inliers(P, m, thr, inl, trace ? &mr : nullptr);
+        // the three per-type counts packed exactly into one double (17 bits each)
+        trace4(-2, (double)(*inl)[0].size() + 131072.0 * (double)(*inl)[1].size() + 17179869184.0 * (double)(*inl)[2].size(), mr);
+        return c;
+    }
     void lsq(const std::vector<std::vector<int>> &sample, Model *m) {
         LmInfo info;
-        if (lm_solve(P, sample.data(), m, &info)) { st.lm_solves++; st.lm_iterations += info.iterations; }
+        if (lm_solve(P, sample.data(), m, &info)) { st.lm_solves++; st.lm_iterations += info.iterations; trace4(-3, info.iterations, info.cost); }
     }
     static void update_best(double sc, const Model &m, int solver, double *best_sc, Model *best, int *best_solver) {
         if (sc < *best_sc) { *best_sc = sc; *best = m; *best_solver = solver; }
@@ -69,7 +81,7 @@ struct Ransac {
         return std::max(mn, r);
     }
     void update_termination(const Model &m) {
-        st.best_num_inliers = get_inliers(P, m, P.thr, &st.inlier_indices);
+        st.best_num_inliers = inliers_traced(m, P.thr, &st.inlier_indices);
         for (int t = 0; t < 3; t++) st.inlier_ratios[t] = P.n > 0 ? (double)st.inlier_indices[t].size() / P.n : 0.0;
         for (int s = 0; s < 2; s++)
             cap[s] = num_required_iterations(st.inlier_ratios, 1.0 - P.opt.success_probability, P.sizes[s],
@@ -93,7 +105,7 @@ struct Ransac {
     }
     void least_squares_fit(const double *thr, int solver, Model *m, bool all_inliers) {
         std::vector<std::vector<int>> inl;
-        get_inliers(P, *m, thr, &inl);
+        inliers_traced(*m, thr, &inl);
         int sz[3];
         for (int t = 0; t < 3; t++) {
             if ((int)inl[t].size() < P.sizes[solver][t]) return;
@@ -119,7 +131,7 @@ struct Ransac {
         double sc = score(m_init, true);
         update_best(sc, m_init, solver, best_score, best, best_solver);
         std::vector<std::vector<int>> base;
-        get_inliers(P, m_init, P.thr, &base);
+        inliers_traced(m_init, P.thr, &base);
         std::vector<int> base_flat;
         for (int t = 0; t < 3; t++) for (int i : base[t]) base_flat.push_back(i + t * P.n);
         const int nonmin = std::max(P.non_min_sample_size,
@@ -132,7 +144,7 @@ struct Ransac {
             Model m = m_init;
             LmInfo info;
             if (!lm_solve(P, sample.data(), &m, &info, true)) continue;
-            st.lm_solves++; st.lm_iterations += info.iterations;
+            st.lm_solves++; st.lm_iterations += info.iterations; trace4(-3, info.iterations, info.cost);
             sc = score(m, true);
             update_best(sc, m, solver, best_score, best, best_solver);
             least_squares_fit(P.thr, solver, &m, false);
