@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmadpose_b200.so")
+LIB_PATH = os.environ.get("MADPOSE_B200_LIB") or os.path.join(_HERE, "libmadpose_b200.so")  # (override: kernel experiments)
 
 KIND_CALIBRATED, KIND_SHARED_FOCAL, KIND_TWO_FOCAL, KIND_SCALE_ONLY = 0, 1, 2, 3
 MODEL_DOUBLES = 17
@@ -124,7 +124,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
     "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
-    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace",
+    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode",
 ]
 
 
@@ -236,6 +236,9 @@ class Context:
                                                     ns, idx.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p),
                                                     cnt.ctypes.data_as(C.c_void_p)))
         return [out[i, :cnt[i]].copy() for i in range(ns)]
+
+    def set_minimal_mode(self, mode):
+        self._check(self.lib.mp_set_minimal_mode(self.ctx, int(mode)))
 
     def set_trace(self, events_per_pair):
         self._check(self.lib.mp_set_trace(self.ctx, int(events_per_pair)))

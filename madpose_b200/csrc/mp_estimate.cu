@@ -98,6 +98,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
     // waits for them: a pair inside a local optimisation sits the rounds out until its lo_kernel publishes it again.
+    const int warp_solvers = c->minimal_mode == 2 || (c->minimal_mode == 0 && n_pairs <= MP_WARP_SOLVER_MAX_PAIRS) ? 1 : 0;
     const bool serial = c->groups_override == 1; // one stream, scan and lo back to back (per-class timing pass)
     int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 749) / 750;
     G = std::max(1, std::min(G, c->groups_override > 0 ? MP_MAX_GROUPS : 8));
@@ -214,7 +215,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         if (serial) MP_CUDA(tick(0));
         sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
         if (serial) MP_CUDA(tick(1));
-        MP_CUDA(launch_minimal_batch(L, dprm, first, count, (long long)std::min(count, std::max(gr[g].act, 0)) * prm->bmax, gs));
+        MP_CUDA(launch_minimal_batch(L, dprm, first, count, (long long)std::min(count, std::max(gr[g].act, 0)) * prm->bmax, kind, c->sm_count, warp_solvers, gs));
         if (serial) MP_CUDA(tick(2));
         if (kind == CALIB) MP_CUDA(launch_score_kind<CALIB>(L, dprm, first, count, tile_cap, smem, gs));
         else if (kind == SHARED) MP_CUDA(launch_score_kind<SHARED>(L, dprm, first, count, tile_cap, smem, gs));
@@ -422,6 +423,12 @@ int mp_read_trace(mp_ctx *c, int pair, double *out, int cap_events, int *n_event
     *n_events = st.trace_n; // may exceed the capacity: the records beyond it were dropped
     const int n = std::min(std::min(st.trace_n, c->trace_cap), cap_events);
     if (n > 0) MP_CUDA(cudaMemcpy(out, A->trace.as<double>() + 2 * (size_t)pair * c->trace_cap, 2 * (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+    return MP_OK;
+}
+int mp_set_minimal_mode(mp_ctx *c, int mode) {
+    using namespace mp;
+    if (!c || mode < 0 || mode > 2) return fail(MP_ERR_ARG, "mp_set_minimal_mode: 0 (automatic), 1 (thread per sample), 2 (warp per sample)");
+    c->minimal_mode = mode;
     return MP_OK;
 }
 int mp_set_batch(mp_ctx *c, int iterations) {

@@ -5,7 +5,14 @@
 
 namespace mp {
 
-cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, cudaStream_t s);
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, int kind,
+                                 int sm_count, int warp_solvers, cudaStream_t s);
+// Batches of at most this many pairs run the point-only minimal solvers that have a warp-per-sample form (6-point shared
+// focal) with ONE WARP per sample -- a round of a small batch holds too few samples to fill the machine with one thread
+// each, and one thread needs ~1.1 ms for a 6-point solve against ~0.1 ms for a warp; larger batches keep one thread per
+// sample (~1.4 x the throughput when every SM is full).  The choice depends on the size of the call only, never on the
+// schedule, so results stay independent of timing (mp_set_minimal_mode overrides it).
+constexpr int MP_WARP_SOLVER_MAX_PAIRS = 64;
 template <int KIND>
 cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, int tile_cap, size_t smem, cudaStream_t s);
 template <int KIND>

@@ -1,8 +1,11 @@
 // K1/K2 translation unit: the per-sample fp64 minimal solvers (compiled once, shared by the
 // stand-alone entry point and the loop's batch kernel) and mp_minimal_solve_batch.
+#include <algorithm>
 #include "mp_host.cuh"
 #include "mp_loop.cuh"
 #include "mp_minimal.cuh"
+#include "mp_warp6.cuh"
+#include "mp_estimate.cuh"
 
 #ifndef MP_MIN_CTAS
 #define MP_MIN_CTAS 12
@@ -101,13 +104,77 @@ __global__ void umeyama_kernel(int n, const double *X, const double *Y, const do
     *out = m;
 }
 
+// ---- K2, shared focal: ONE WARP per point-solver sample (mp_warp6.cuh).  Stand-alone form (mp_minimal_solve_batch):
+// the candidates' tail (triangulation + depth fits) runs one candidate per lane, survivors are compacted in order.
+constexpr int W6_WARPS = 4;
+__device__ inline void warp6_load_sample(Warp6Work &W, const Match64 *M, const int *idx, int lane) {
+    if (lane < 6) {
+        const Match64 m = M[idx[lane]];
+        W.x1[lane][0] = m.x0x; W.x1[lane][1] = m.x0y; W.x1[lane][2] = 1.0;
+        W.x2[lane][0] = m.x1x; W.x2[lane][1] = m.x1y; W.x2[lane][2] = 1.0;
+    }
+    __syncwarp();
+}
+__global__ void __launch_bounds__(W6_WARPS * 32) minimal6_warp_kernel(const PairConst *pcp, const Match64 *M, int n_samples, const int *idx,
+                                                                      unsigned mflags, int max_models, Model *out, int *counts, Model *scratch) {
+    __shared__ Warp6Work work[W6_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const PairConst &pc = *pcp;
+    Warp6Work &W = work[warp];
+    for (int s = blockIdx.x * W6_WARPS + warp; s < n_samples; s += gridDim.x * W6_WARPS) {
+        warp6_load_sample(W, M + pc.off, idx + (size_t)s * 6, lane);
+        Model *cand = scratch + (size_t)s * kMaxModelsAny;
+        const int c = warp_relpose_6pt(W, cand, lane);
+        __syncwarp();
+        bool ok = false;
+        Model m;
+        if (lane < c) { m = cand[lane]; ok = minimal_tail_ni(pc, M + pc.off, idx + (size_t)s * 6, mflags, &m); }
+        const unsigned keep = __ballot_sync(0xffffffffu, ok);
+        const int k = __popc(keep & ((1u << lane) - 1u));
+        if (ok && k < max_models) out[(size_t)s * max_models + k] = m;
+        if (lane == 0) counts[s] = min(__popc(keep), max_models);
+        __syncwarp();
+    }
+}
+// the loop's form: the point-solver samples of the round (list 1 of the sample kernel); candidates go to the model
+// slots and to the candidate list of minimal_tail_kernel, exactly as minimal_batch_kernel leaves them
+#ifndef W6_MIN_CTAS
+#define W6_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(W6_WARPS * 32, W6_MIN_CTAS) minimal6_warp_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    __shared__ Warp6Work work[W6_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = first / L.gsz;
+    const int n1 = L.n_items[2 * grp + 1];
+    Warp6Work &W = work[warp];
+    for (int g = blockIdx.x * W6_WARPS + warp; g < n1; g += gridDim.x * W6_WARPS) {
+        const int item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + g];
+        const int p = first + item / LP_BMAX, b = item % LP_BMAX;
+        PairWork &Wk = L.wk[p];
+        const PairConst &pc = L.pc[p];
+        warp6_load_sample(W, L.M + pc.off, Wk.idx[b], lane);
+        Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
+        const int c = warp_relpose_6pt(W, out, lane);
+        if (lane == 0) {
+            Wk.count[b] = c;
+            if (c > 0) {
+                const int base = atomicAdd(L.n_cand + grp, c);
+                int *cl = L.cand + (size_t)first * LP_BMAX * LP_MM;
+                for (int j = 0; j < c; j++) cl[base + j] = item * LP_MM + j;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
 // sample kernel filled (solver 0 first, solver 1 from the next multiple of 32: a warp runs one solver only)
-__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count, int skip1) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     const int grp = first / L.gsz;
-    const int n0 = L.n_items[2 * grp], n1 = L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
+    // skip1: the point-solver samples are solved by the warp-per-sample kernel
+    const int n0 = L.n_items[2 * grp], n1 = skip1 ? 0 : L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
     int item;
     if (g < n0) item = L.items[(size_t)first * LP_BMAX + g];
     else if (g >= n0p && g < n0p + n1) item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + (g - n0p)];
@@ -180,9 +247,16 @@ __global__ void __launch_bounds__(64) minimal_pack_kernel(LoopBuffers L, const L
 // items_bound: upper bound of the samples of this round (pairs of the group that are not done x batch cap): the item
 // and candidate lists are dense, so the grids only have to cover them (45000 empty CTAs cost 0.13 ms in a round that
 // has one pair left)
-cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, cudaStream_t s) {
+cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, int kind,
+                                 int sm_count, int warp_solvers, cudaStream_t s) {
     const long long ib = items_bound > 0 ? items_bound : 1;
-    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
+    const int warp6 = (kind == SHARED && warp_solvers) ? 1 : 0;
+    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count, warp6);
+    if (warp6) { // grid-stride over the list: enough CTAs to fill the machine, no more than the list can use
+        const long long want = (ib + W6_WARPS - 1) / W6_WARPS;
+        const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count * 8));
+        minimal6_warp_batch_kernel<<<grid, W6_WARPS * 32, 0, s>>>(L, dprm, first, count);
+    }
     // worst case of the candidate list: every sample of the round is a point-solver sample with LP_MM candidates; the
     // threads beyond the actual count exit at once
     minimal_tail_kernel<<<(unsigned)((ib * LP_MM + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
@@ -214,6 +288,14 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
     MP_CUDA(c->d_misc.reserve((size_t)n_samples * sizeof(int)));
     MP_CUDA(cudaMemcpyAsync(c->d_idx.p, sample_idx, (size_t)n_samples * k * sizeof(int), cudaMemcpyHostToDevice, s));
     MP_CUDA(cudaEventRecord(c->ev[0], s));
+    if (kk == SHARED && solver_idx == 1 && c->minimal_mode != 1 && (c->minimal_mode == 2 || n_samples <= MP_WARP_SOLVER_MAX_PAIRS * LP_BDEF)) {
+        // one warp per sample: the path small batches take (mp_set_minimal_mode)
+        MP_CUDA(c->d_work.reserve((size_t)n_samples * kMaxModelsAny * sizeof(Model)));
+        const unsigned grid = (unsigned)std::max(1, std::min((n_samples + W6_WARPS - 1) / W6_WARPS, c->sm_count * 8));
+        minimal6_warp_kernel<<<grid, W6_WARPS * 32, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), n_samples,
+                                                             c->d_idx.as<int>(), minimal_flags(*cfg), mm, c->d_models.as<Model>(),
+                                                             c->d_misc.as<int>(), c->d_work.as<Model>());
+    } else
     minimal_kernel<<<(n_samples + 63) / 64, 64, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), solver_idx, k,
                                                         n_samples, c->d_idx.as<int>(), minimal_flags(*cfg), mm,
                                                         c->d_models.as<Model>(), c->d_misc.as<int>());

@@ -313,6 +313,21 @@ def test_knob_and_helper_argument_checks(ctx):
         ctx.pose_errors(np.zeros((2, 4, 4)), np.zeros((3, 3, 3)), np.zeros((2, 3)))
 
 
+@pytest.mark.parametrize("mode", [1, 2])
+def test_minimal_modes_whole_path(ctx, oracle, mode):
+    """Both forms of the 6-point solver (one thread / one warp per sample) through the whole path against the oracle."""
+    ps = [problem(1, p=100 + i, n=800) for i in range(6)]
+    kind, opt, cfg = 1, ps[0][2], ps[0][3]
+    pairs = [q[1] for q in ps]
+    mo, so, io = oracle.estimate_batch(kind, pairs, opt, cfg, threads=6)
+    ctx.set_minimal_mode(mode)
+    try:
+        mg, sg, ig = ctx.estimate_batch(kind, pairs, opt, cfg)
+        compare(oracle, kind, pairs, opt, cfg, mo, so, io, mg, sg, ig, max_forks=1, ctx=ctx)
+    finally:
+        ctx.set_minimal_mode(0)
+
+
 def test_schedule_invariance(ctx):
     """The result of a pair must not depend on how the device loop is scheduled: iterations speculated per round
     (mp_set_batch), number of stream groups (mp_set_groups; 1 = everything on one stream), i.e. on which round a pair

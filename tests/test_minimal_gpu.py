@@ -24,14 +24,21 @@ def _match(a, b):
     return out
 
 
+@pytest.mark.parametrize("mode", [1, 2])   # one thread per sample / one warp per sample (mp_set_minimal_mode)
 @pytest.mark.parametrize("config", [0, 1, 2])
 @pytest.mark.parametrize("solver", [0, 1])
-def test_minimal_solvers_match_oracle(ctx, oracle, config, solver):
+def test_minimal_solvers_match_oracle(ctx, oracle, config, solver, mode):
     d, pair, opt, cfg, keep = problem(config, p=5)
     kind = d["kind"]
+    if mode == 2 and not (kind == 1 and solver == 1):
+        pytest.skip("no warp-per-sample form of this solver")
     S = _samples(d, pair.n, K[kind][solver], 400, 100 * config + solver)
     ref = oracle.minimal_solve(kind, pair, opt, cfg, solver, S)
-    got = ctx.minimal_solve_batch(kind, pair, opt, cfg, solver, S)
+    ctx.set_minimal_mode(mode)
+    try:
+        got = ctx.minimal_solve_batch(kind, pair, opt, cfg, solver, S)
+    finally:
+        ctx.set_minimal_mode(0)
     errs, count_mismatch = [], 0
     for a, b in zip(ref, got):
         if len(a) != len(b):
