@@ -135,11 +135,14 @@ int mp_set_groups(mp_ctx *ctx, int groups);
 /* Upper bound of the RANSAC iterations speculated per pair per round (1..256; 0 = default 128).  A pair starts with 64
  * and doubles its batch after every round that found no new best model.  Results do not depend on it. */
 int mp_set_batch(mp_ctx *ctx, int iterations);
-/* Which form of the point-only minimal solvers runs (6-point shared focal today): 0 = automatic (one warp per sample
- * for calls of at most 64 pairs, whose rounds cannot fill the machine with one thread per sample; one thread per sample
- * otherwise), 1 = always one thread per sample, 2 = always one warp per sample.  The two forms agree to rounding
- * (each within the parity tolerances against the oracle); for a given mode results never depend on the schedule. */
+/* Which form of the point-only minimal solvers that have both runs (6-point shared focal today): 0 = automatic (one
+ * warp per sample), 1 = one thread per sample, 2 = one warp per sample.  The two forms agree to rounding (each within
+ * the parity tolerances against the oracle); for a given mode results never depend on the schedule. */
 int mp_set_minimal_mode(mp_ctx *ctx, int mode);
+/* Experiments: in automatic mode the point-solver samples of RANSAC iterations >= `iteration` take the warp-per-sample
+ * form and the earlier ones the thread-per-sample form (default 0: all of them the warp form).  -1 restores the default.  A function of the iteration index only, so results
+ * do not depend on the schedule; different values give results that agree to rounding. */
+int mp_set_warp_from_iteration(mp_ctx *ctx, int iteration);
 /* Parity forensics: with events_per_pair > 0 the next estimate calls record, per pair and in chronological order, one
  * {iteration, score} record for every iteration whose best hypothesis was re-scored in fp64 and one {-1, score} record
  * for every ScoreModel inside LocalOptimization / the final least squares (hybrid_ransac.h:383-482, 186-203).

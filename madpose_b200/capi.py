@@ -124,7 +124,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
     "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
-    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode",
+    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode", "mp_set_warp_from_iteration",
 ]
 
 
@@ -239,6 +239,9 @@ class Context:
 
     def set_minimal_mode(self, mode):
         self._check(self.lib.mp_set_minimal_mode(self.ctx, int(mode)))
+
+    def set_warp_from_iteration(self, iteration):
+        self._check(self.lib.mp_set_warp_from_iteration(self.ctx, int(iteration)))
 
     def set_trace(self, events_per_pair):
         self._check(self.lib.mp_set_trace(self.ctx, int(events_per_pair)))

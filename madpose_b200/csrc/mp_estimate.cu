@@ -98,7 +98,12 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never
     // waits for them: a pair inside a local optimisation sits the rounds out until its lo_kernel publishes it again.
-    const int warp_solvers = c->minimal_mode == 2 || (c->minimal_mode == 0 && n_pairs <= MP_WARP_SOLVER_MAX_PAIRS) ? 1 : 0;
+    // which point-solver samples take the warp-per-sample form (kinds that have one): all of them for small calls,
+    // the late iterations (>= MP_WARP_FROM_IT, i.e. the pairs that make up the ramp-down of a large batch) otherwise
+    const unsigned warp_from = c->minimal_mode == 2 ? 0u : (c->minimal_mode == 1 ? 0xffffffffu :
+                               (n_pairs <= MP_WARP_SOLVER_MAX_PAIRS ? 0u : (c->warp_from_it >= 0 ? (unsigned)c->warp_from_it : MP_WARP_FROM_IT)));
+    prm->warp_from_it = (kind == SHARED) ? warp_from : 0xffffffffu;
+    const int warp_solvers = prm->warp_from_it != 0xffffffffu ? 1 : 0;
     const bool serial = c->groups_override == 1; // one stream, scan and lo back to back (per-class timing pass)
     int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 749) / 750;
     G = std::max(1, std::min(G, c->groups_override > 0 ? MP_MAX_GROUPS : 8));
@@ -108,7 +113,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.misc.reserve(128 + 28 * MP_MAX_GROUPS));
     MP_CUDA(A.cand.reserve(slots * sizeof(int)));
     MP_CUDA(A.cand_ok.reserve(slots));
-    MP_CUDA(A.items.reserve(2 * (size_t)n_pairs * LP_BMAX * sizeof(int)));
+    MP_CUDA(A.items.reserve(3 * (size_t)n_pairs * LP_BMAX * sizeof(int)));
     MP_CUDA(A.h_active.reserve(4 * (2 + 2 * SLOTS) * MP_MAX_GROUPS));
     MP_CUDA(A.lo_req.reserve(n_pairs * sizeof(int)));
     int *h_active = A.h_active.as<int>(), *h_iter = h_active + G, *h_side = h_active + 2 * G; // h_side[2 * (g * SLOTS + k)] = {pairs not done, pairs handed back so far}
@@ -148,6 +153,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     L.n_iter = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 4 * MP_MAX_GROUPS);
     L.n_items = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 8 * MP_MAX_GROUPS);
     L.n_ret = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 16 * MP_MAX_GROUPS);
+    L.n_items_w = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 20 * MP_MAX_GROUPS);
     L.n_cand = reinterpret_cast<int *>(A.misc.as<char>() + 128 + 24 * MP_MAX_GROUPS);
     L.cand = A.cand.as<int>(); L.cand_ok = A.cand_ok.as<unsigned char>();
     MP_CUDA(cudaMemsetAsync(L.n_ret, 0, G * sizeof(int), s));
@@ -211,6 +217,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         const int round = (int)(++gr[g].round);
         MP_CUDA(cudaMemsetAsync(L.n_iter + g, 0, sizeof(int), gs));
         MP_CUDA(cudaMemsetAsync(L.n_items + 2 * g, 0, 2 * sizeof(int), gs));
+        MP_CUDA(cudaMemsetAsync(L.n_items_w + g, 0, sizeof(int), gs));
         MP_CUDA(cudaMemsetAsync(L.n_cand + g, 0, sizeof(int), gs));
         if (serial) MP_CUDA(tick(0));
         sample_kernel<<<(count + SMP_WARPS - 1) / SMP_WARPS, SMP_WARPS * 32, 0, gs>>>(L, dprm, first, count);
@@ -346,6 +353,7 @@ int mp_lm_batch(mp_ctx *c, int kind, const mp_pair *pair, const mp_options *opt,
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     LoopParams *prm = A.h_prm.as<LoopParams>();
     prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = 1; prm->bmax = LP_BMAX; prm->b_after_lo = LP_BMAX / 4; prm->guard = 1e-3;
+    prm->warp_from_it = 0xffffffffu;
     MP_CUDA(c->d_models.reserve(2 * (size_t)n_problems * sizeof(Model)));
     MP_CUDA(c->d_idx.reserve(((size_t)nidx + 3 * (size_t)n_problems + 8) * sizeof(int)));
     MP_CUDA(c->d_scores64.reserve(4 * (size_t)n_problems * sizeof(double)));
@@ -429,6 +437,12 @@ int mp_set_minimal_mode(mp_ctx *c, int mode) {
     using namespace mp;
     if (!c || mode < 0 || mode > 2) return fail(MP_ERR_ARG, "mp_set_minimal_mode: 0 (automatic), 1 (thread per sample), 2 (warp per sample)");
     c->minimal_mode = mode;
+    return MP_OK;
+}
+int mp_set_warp_from_iteration(mp_ctx *c, int iteration) {
+    using namespace mp;
+    if (!c || iteration < -1) return fail(MP_ERR_ARG, "mp_set_warp_from_iteration: -1 (default) or an iteration index >= 0");
+    c->warp_from_it = iteration;
     return MP_OK;
 }
 int mp_set_batch(mp_ctx *c, int iterations) {

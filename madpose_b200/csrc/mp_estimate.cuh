@@ -7,12 +7,16 @@ namespace mp {
 
 cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, int kind,
                                  int sm_count, int warp_solvers, cudaStream_t s);
-// Batches of at most this many pairs run the point-only minimal solvers that have a warp-per-sample form (6-point shared
-// focal) with ONE WARP per sample -- a round of a small batch holds too few samples to fill the machine with one thread
-// each, and one thread needs ~1.1 ms for a 6-point solve against ~0.1 ms for a warp; larger batches keep one thread per
-// sample (~1.4 x the throughput when every SM is full).  The choice depends on the size of the call only, never on the
-// schedule, so results stay independent of timing (mp_set_minimal_mode overrides it).
-constexpr int MP_WARP_SOLVER_MAX_PAIRS = 64;
+// The point-only minimal solvers that have a warp-per-sample form (6-point shared focal, mp_warp6.cuh) run with ONE WARP
+// per sample: no thread-private arrays (the thread-per-sample form keeps 17 KB of local memory per thread) and ~0.1 ms
+// instead of ~1.1 ms for one solve.  The loop's kernel runs 12 warps per CTA, one CTA per SM, with CTA barriers between
+// the solver's stages so that all warps of an SM execute the same stage's code at the same time -- the solver is
+// ~170 KB of instructions and free-running warps thrash the instruction cache.  Measured on configs[1]
+// (tools/exp_warp_from.py): thread per sample 167.7 ms/step; warp per sample free-running 194.7; in lockstep 137.9
+// (8 warps per CTA: 145.9, 16: 137.1).  mp_set_minimal_mode / mp_set_warp_from_iteration select the forms for
+// experiments; for a given setting results never depend on the schedule.
+constexpr int MP_WARP_SOLVER_MAX_PAIRS = 1 << 30; // (calls up to this size use the warp form for every iteration)
+constexpr unsigned MP_WARP_FROM_IT = 0u;
 template <int KIND>
 cudaError_t launch_score_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, int tile_cap, size_t smem, cudaStream_t s);
 template <int KIND>

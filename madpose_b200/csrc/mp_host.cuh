@@ -77,6 +77,7 @@ struct mp_ctx {
     double class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     int groups_override = 0, last_groups = 1; // 0 = automatic
+    int warp_from_it = -1;                    // experiments: override of MP_WARP_FROM_IT (-1 = default)
     int minimal_mode = 0;                     // mp_set_minimal_mode: 0 automatic, 1 one thread per sample, 2 one warp per sample
     int trace_cap = 0;                        // mp_set_trace: events kept per pair (0 = tracing off)
     int batch_override = 0;                   // speculated iterations per pair per round, 0 = LP_BMAX

@@ -36,6 +36,8 @@ struct LoopParams {
     int b_after_lo; // batch length of the first round and of the first round after a local optimisation (doubles every
                     // quiet round up to bmax)
     double guard; // relative guard band of the fp32 score filter
+    unsigned warp_from_it; // point-solver samples of iterations >= this are solved with one warp per sample (kinds that
+                           // have such a solver); 0 = all of them, 0xffffffff = none
 };
 
 struct alignas(128) PairState { // 128-byte aligned: no cache line is shared between pairs (see sample_kernel)
@@ -88,7 +90,8 @@ struct LoopBuffers {
     unsigned char *cand_ok; // per model slot: did the candidate survive its tail
     int *n_ret;     // per group: pairs handed back to PH_ITER by lo_kernel launches so far (cumulative)
     int *n_items;   // per group: [2] number of samples of this round per minimal solver (reset every round)
-    int *items;     // [2][n_pairs * LP_BMAX] samples of this round, (pair - first) * LP_BMAX + b, grouped per solver so that
+    int *n_items_w; // per group: point-solver samples of this round routed to the warp-per-sample kernel (third list)
+    int *items;     // [3][n_pairs * LP_BMAX] samples of this round, (pair - first) * LP_BMAX + b, grouped per solver so that
                     // the warps of the minimal kernel run ONE solver each (a group uses its own slice [first * LP_BMAX, ...))
     int n_pairs;
     int *lo_req;    // per pair: 0, or the round whose scan asked for a local optimisation / the final stage

@@ -192,14 +192,22 @@ __global__ void __launch_bounds__(SMP_WARPS * 32) sample_kernel(LoopBuffers L, c
         }
         endA = sa.position();
     }
-    int n1 = 0; // iterations that drew solver 1
-    for (unsigned b = 0; b < len; b++) n1 += sol[b];
-    { // hand the samples to the minimal kernel, one list per solver
-        const int g = p / L.gsz, n0 = (int)len - n1;
+    // Hand the samples to the minimal kernels: one list per solver, and the point-solver samples of the iterations
+    // >= prm.warp_from_it in a third list that the warp-per-sample kernel solves.  Which form solves a sample depends
+    // on its (pair, iteration) only -- never on the schedule.
+    const unsigned it0i = S.it;
+    int n1 = 0, n2 = 0;
+    for (unsigned b = 0; b < len; b++) {
+        if (sol[b] == 1) { if (it0i + b >= prm.warp_from_it) n2++; else n1++; }
+    }
+    {
+        const int g = p / L.gsz, n0 = (int)len - n1 - n2;
         int o0i = n0 > 0 ? atomicAdd(L.n_items + 2 * g, n0) : 0, o1i = n1 > 0 ? atomicAdd(L.n_items + 2 * g + 1, n1) : 0;
+        int o2i = n2 > 0 ? atomicAdd(L.n_items_w + g, n2) : 0;
         int *it0 = L.items + (size_t)first * LP_BMAX, *it1 = L.items + (size_t)(L.n_pairs + first) * LP_BMAX;
+        int *it2 = L.items + (size_t)(2 * L.n_pairs + first) * LP_BMAX;
         for (unsigned b = 0; b < len; b++) {
-            if (sol[b] == 1) it1[o1i++] = q * LP_BMAX + (int)b;
+            if (sol[b] == 1) { if (it0i + b >= prm.warp_from_it) it2[o2i++] = q * LP_BMAX + (int)b; else it1[o1i++] = q * LP_BMAX + (int)b; }
             else it0[o0i++] = q * LP_BMAX + (int)b;
         }
     }

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(W6_WARPS * 32) minimal6_warp_kernel(const Pair
     for (int s = blockIdx.x * W6_WARPS + warp; s < n_samples; s += gridDim.x * W6_WARPS) {
         warp6_load_sample(W, M + pc.off, idx + (size_t)s * 6, lane);
         Model *cand = scratch + (size_t)s * kMaxModelsAny;
-        const int c = warp_relpose_6pt(W, cand, lane);
+        const int c = warp_relpose_6pt<false>(W, cand, lane);
         __syncwarp();
         bool ok = false;
         Model m;
@@ -138,24 +138,27 @@ __global__ void __launch_bounds__(W6_WARPS * 32) minimal6_warp_kernel(const Pair
 }
 // the loop's form: the point-solver samples of the round (list 1 of the sample kernel); candidates go to the model
 // slots and to the candidate list of minimal_tail_kernel, exactly as minimal_batch_kernel leaves them
-#ifndef W6_MIN_CTAS
-#define W6_MIN_CTAS 4
+#ifndef W6B_WARPS
+#define W6B_WARPS 12   // warps per CTA of the loop's kernel: one CTA per SM, stages in lockstep
 #endif
-__global__ void __launch_bounds__(W6_WARPS * 32, W6_MIN_CTAS) minimal6_warp_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
-    __shared__ Warp6Work work[W6_WARPS];
+__global__ void __launch_bounds__(W6B_WARPS * 32, 1) minimal6_warp_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    extern __shared__ __align__(16) unsigned char w6_smem[];
+    Warp6Work *work = reinterpret_cast<Warp6Work *>(w6_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int grp = first / L.gsz;
-    const int n1 = L.n_items[2 * grp + 1];
+    const int n1 = L.n_items_w[grp];
     Warp6Work &W = work[warp];
-    for (int g = blockIdx.x * W6_WARPS + warp; g < n1; g += gridDim.x * W6_WARPS) {
-        const int item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + g];
+    for (int g0 = blockIdx.x * W6B_WARPS; g0 < n1; g0 += gridDim.x * W6B_WARPS) { // uniform trip count over the CTA
+        const int g = g0 + warp;
+        const bool valid = g < n1;
+        const int item = valid ? L.items[(size_t)(2 * L.n_pairs + first) * LP_BMAX + g] : 0;
         const int p = first + item / LP_BMAX, b = item % LP_BMAX;
         PairWork &Wk = L.wk[p];
         const PairConst &pc = L.pc[p];
-        warp6_load_sample(W, L.M + pc.off, Wk.idx[b], lane);
+        if (valid) warp6_load_sample(W, L.M + pc.off, Wk.idx[b], lane);
         Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
-        const int c = warp_relpose_6pt(W, out, lane);
-        if (lane == 0) {
+        const int c = warp_relpose_6pt<true>(W, out, lane, valid);
+        if (lane == 0 && valid) {
             Wk.count[b] = c;
             if (c > 0) {
                 const int base = atomicAdd(L.n_cand + grp, c);
@@ -169,12 +172,11 @@ __global__ void __launch_bounds__(W6_WARPS * 32, W6_MIN_CTAS) minimal6_warp_batc
 
 // ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
 // sample kernel filled (solver 0 first, solver 1 from the next multiple of 32: a warp runs one solver only)
-__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count, int skip1) {
+__global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     const int grp = first / L.gsz;
-    // skip1: the point-solver samples are solved by the warp-per-sample kernel
-    const int n0 = L.n_items[2 * grp], n1 = skip1 ? 0 : L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
+    const int n0 = L.n_items[2 * grp], n1 = L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
     int item;
     if (g < n0) item = L.items[(size_t)first * LP_BMAX + g];
     else if (g >= n0p && g < n0p + n1) item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + (g - n0p)];
@@ -224,8 +226,9 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_tail_kernel(LoopBuffe
 __global__ void __launch_bounds__(64) minimal_pack_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     const int grp = first / L.gsz;
-    if (g >= L.n_items[2 * grp + 1]) return;
-    const int item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + g];
+    const int n1 = L.n_items[2 * grp + 1], n2 = L.n_items_w[grp]; // both point-solver lists
+    if (g >= n1 + n2) return;
+    const int item = g < n1 ? L.items[(size_t)(L.n_pairs + first) * LP_BMAX + g] : L.items[(size_t)(2 * L.n_pairs + first) * LP_BMAX + (g - n1)];
     const int p = first + item / LP_BMAX, b = item % LP_BMAX;
     const PairConst &pc = L.pc[p];
     PairWork &W = L.wk[p];
@@ -250,12 +253,15 @@ __global__ void __launch_bounds__(64) minimal_pack_kernel(LoopBuffers L, const L
 cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int first, int count, long long items_bound, int kind,
                                  int sm_count, int warp_solvers, cudaStream_t s) {
     const long long ib = items_bound > 0 ? items_bound : 1;
-    const int warp6 = (kind == SHARED && warp_solvers) ? 1 : 0;
-    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count, warp6);
+    const int warp6 = (kind == SHARED && warp_solvers) ? 1 : 0; // lists routed to it are empty otherwise
+    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
     if (warp6) { // grid-stride over the list: enough CTAs to fill the machine, no more than the list can use
-        const long long want = (ib + W6_WARPS - 1) / W6_WARPS;
-        const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count * 8));
-        minimal6_warp_batch_kernel<<<grid, W6_WARPS * 32, 0, s>>>(L, dprm, first, count);
+        const long long want = (ib + W6B_WARPS - 1) / W6B_WARPS;
+        const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count));
+        static const cudaError_t attr = cudaFuncSetAttribute(minimal6_warp_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                             (int)(W6B_WARPS * sizeof(Warp6Work)));
+        if (attr != cudaSuccess) return attr;
+        minimal6_warp_batch_kernel<<<grid, W6B_WARPS * 32, W6B_WARPS * sizeof(Warp6Work), s>>>(L, dprm, first, count);
     }
     // worst case of the candidate list: every sample of the round is a point-solver sample with LP_MM candidates; the
     // threads beyond the actual count exit at once
@@ -288,7 +294,7 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
     MP_CUDA(c->d_misc.reserve((size_t)n_samples * sizeof(int)));
     MP_CUDA(cudaMemcpyAsync(c->d_idx.p, sample_idx, (size_t)n_samples * k * sizeof(int), cudaMemcpyHostToDevice, s));
     MP_CUDA(cudaEventRecord(c->ev[0], s));
-    if (kk == SHARED && solver_idx == 1 && c->minimal_mode != 1 && (c->minimal_mode == 2 || n_samples <= MP_WARP_SOLVER_MAX_PAIRS * LP_BDEF)) {
+    if (kk == SHARED && solver_idx == 1 && c->minimal_mode != 1 && true) {
         // one warp per sample: the path small batches take (mp_set_minimal_mode)
         MP_CUDA(c->d_work.reserve((size_t)n_samples * kMaxModelsAny * sizeof(Model)));
         const unsigned grid = (unsigned)std::max(1, std::min((n_samples + W6_WARPS - 1) / W6_WARPS, c->sm_count * 8));

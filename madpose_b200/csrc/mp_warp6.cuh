@@ -279,12 +279,22 @@ __device__ inline int group_motion_from_essential(const Warp6Work &W, const doub
 
 // The solver.  Sample points (x, y, 1) must be in W.x1 / W.x2.  Writes up to 15 candidates (R, t, focal; scale 1,
 // offsets 0) to out (global or shared memory) and returns their number (uniform over the warp).
-__device__ inline int warp_relpose_6pt(Warp6Work &W, Model *out, int lane) {
-    warp6_nullspace(W, lane);
-    if (!warp6_build(W, lane)) return 0;
-    warp6_dets(W, lane);
-    warp6_coefs(W, lane);
-    const int nr = warp_real_roots<15>(W.coef, 15, W.roots, W.u.poly, true, lane);
+// LOCKSTEP: all warps of the CTA call it together (valid = this warp has a sample) and meet at a CTA barrier between
+// the stages, so that they execute the same stage's code at the same time (the solver is ~170 KB of instructions).
+template <bool LOCKSTEP> __device__ inline int warp_relpose_6pt(Warp6Work &W, Model *out, int lane, bool valid = true) {
+    if (valid) warp6_nullspace(W, lane);
+    if (LOCKSTEP) __syncthreads();
+    bool ok = valid;
+    if (ok) ok = warp6_build(W, lane);
+    if (LOCKSTEP) __syncthreads();
+    if (ok) warp6_dets(W, lane);
+    if (LOCKSTEP) __syncthreads();
+    int nr = 0;
+    if (ok) {
+        warp6_coefs(W, lane);
+        nr = warp_real_roots<15>(W.coef, 15, W.roots, W.u.poly, true, lane);
+    }
+    if (LOCKSTEP) __syncthreads();
     __syncwarp();
     int n = 0;
     const int g = lane / 10, r = lane % 10;

@@ -1,19 +1,18 @@
-"""Experiment: step time of configs[1] versus the number of stream groups."""
-import sys, time, os
+#!/usr/bin/env python
+"""experiment: step time of a config vs stream groups and speculation batch cap: exp_groups.py [config]"""
+import os, sys
+import numpy as np
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import bench
-from madpose_b200 import capi
-kind, pairs, opt, cfg, keep = bench.make_batch(1500, 0)
+from madpose_b200 import capi, workload
+config = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+kind, pairs, opt, cfg, keep = workload.make_batch(config, workload.CONFIG_INFO[config]["pairs"])
 ctx = capi.Context(0)
 ctx.upload_batch(kind, pairs, opt)
-B = int(os.environ.get("MP_BATCH", "0"))
-print("MP_LO_THREADS", os.environ.get("MP_LO_THREADS"))
-ctx.set_batch(B)
-for G in [int(x) for x in sys.argv[1:]] or [16, 32, 64, 128, 256]:
-    ctx.set_groups(G)
-    ctx.estimate_resident(opt, cfg)
-    ts = []
-    for _ in range(3):
-        t0 = time.perf_counter(); ctx.estimate_resident(opt, cfg); wall = time.perf_counter() - t0
-        ts.append((ctx.last_timing()[1], wall * 1e3))
-    print("batch", B, "groups", G, "device ms", [round(t[0], 1) for t in ts], "wall ms", [round(t[1], 1) for t in ts], "launches", ctx.last_timing()[2], flush=True)
+for g, b in [(0, 0), (1, 0), (2, 0), (3, 0), (4, 0), (6, 0), (1, 256), (2, 256), (2, 64), (3, 64)]:
+    ctx.set_groups(g); ctx.set_batch(b)
+    ms = []
+    for _ in range(4):
+        ctx.estimate_resident(opt, cfg)
+        ms.append(ctx.last_timing()[1])
+    print("groups", g, "batch", b, "ms/step", round(float(np.median(ms[1:])), 1), "rounds", ctx.last_breakdown()[1])
