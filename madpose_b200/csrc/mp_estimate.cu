@@ -89,7 +89,10 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(A.h_prm.reserve(sizeof(LoopParams)));
     MP_CUDA(A.h_active.reserve(4 * MP_MAX_GROUPS));
     LoopParams *prm = A.h_prm.as<LoopParams>();
-    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; prm->bmax = c->batch_override > 0 ? c->batch_override : LP_BDEF;
+    prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; // speculated iterations per pair per round: 128, or 256 for long loops (an iteration budget of thousands: every round
+    // costs a fixed launch + solve latency; measured on configs[3], 64 pairs x ~7600 iterations: 176 -> 164 ms/step)
+    prm->bmax = c->batch_override > 0 ? c->batch_override
+                                      : (std::max(opt->max_num_iterations, opt->min_num_iterations) >= 4096 ? LP_BMAX : LP_BDEF);
     {
         const char *e = getenv("MP_B_AFTER_LO"); // experiments
         const int v = e ? atoi(e) : 0;
@@ -105,7 +108,9 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     prm->warp_from_it = (kind == SHARED) ? warp_from : 0xffffffffu;
     const int warp_solvers = prm->warp_from_it != 0xffffffffu ? 1 : 0;
     const bool serial = c->groups_override == 1; // one stream, scan and lo back to back (per-class timing pass)
-    int G = c->groups_override > 0 ? c->groups_override : (n_pairs + 749) / 750;
+    // automatic: about 750 pairs per group, at least two groups from 16 pairs on (two round pipelines overlap each
+    // other's launch gaps; measured on configs[3], 64 pairs: 187 -> 176 ms/step)
+    int G = c->groups_override > 0 ? c->groups_override : std::max((n_pairs + 749) / 750, n_pairs >= 16 ? 2 : 1);
     G = std::max(1, std::min(G, c->groups_override > 0 ? MP_MAX_GROUPS : 8));
     const int gsz = (n_pairs + G - 1) / G;
     G = (n_pairs + gsz - 1) / gsz;
