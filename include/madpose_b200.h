@@ -124,6 +124,20 @@ int mp_estimate_batch(mp_ctx *ctx, int kind, int n_pairs, const mp_pair *pairs, 
 int mp_upload_batch(mp_ctx *ctx, int kind, int n_pairs, const mp_pair *pairs, const mp_options *opt);
 int mp_estimate_resident(mp_ctx *ctx, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
                          mp_stats *out_stats, int32_t *out_inliers);
+/* ---- several GPUs of one node inside the library.  Pairs are independent: the batch is dealt to the
+ * devices by decreasing match count (snake order), every device runs its share through mp_estimate_batch on its own
+ * context and host thread, results are scattered back in the caller's order (same buffers / layout as
+ * mp_estimate_batch).  No inter-GPU traffic.  Contexts are created on first use and kept for the process lifetime.
+ * A pair's result does not depend on which device ran it or on n_devices. */
+int mp_estimate_batch_multi(int n_devices, const int *devices, int kind, int n_pairs, const mp_pair *pairs,
+                            const mp_options *opt, const mp_config *cfg, mp_model *out_models, mp_stats *out_stats,
+                            int32_t *out_inliers);
+/* The same for a batch that mixes estimator kinds (BASELINE.json configs[4]): kinds[p] in 0..3, opt_by_kind[4] = the
+ * options of each kind (entries of absent kinds are not read).  The kinds run concurrently on every device. */
+int mp_estimate_mixed_multi(int n_devices, const int *devices, int n_pairs, const int *kinds, const mp_pair *pairs,
+                            const mp_options *opt_by_kind, const mp_config *cfg, mp_model *out_models,
+                            mp_stats *out_stats, int32_t *out_inliers);
+int mp_device_count(void); /* CUDA devices visible to the process (0 without a driver) */
 /* per kernel class of the last estimate call: device ms (CUDA events) and launch counts for
  * {sampling, minimal solvers, fp32 scoring, decide (fp64 re-score + inliers + LO/LM)}; rounds */
 int mp_last_breakdown(mp_ctx *ctx, double *class_ms4, int *class_launches4, int *rounds);

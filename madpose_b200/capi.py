@@ -124,7 +124,7 @@ def pack_model(R, t, scale=1.0, o0=0.0, o1=0.0, f0=1.0, f1=1.0):
 _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
     "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
-    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode", "mp_set_warp_from_iteration",
+    "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode", "mp_set_warp_from_iteration", "mp_estimate_batch_multi", "mp_estimate_mixed_multi", "mp_device_count",
 ]
 
 
@@ -140,6 +140,35 @@ def load_library(path=LIB_PATH):
         getattr(lib, s).restype = C.c_int
     lib.mp_destroy.restype = None
     return lib
+
+
+def estimate_batch_multi(devices, kind, pairs, opt, cfg, lib=None, kinds=None, opt_by_kind=None):
+    """mp_estimate_batch_multi / mp_estimate_mixed_multi (kinds = per-pair kinds, opt_by_kind = dict kind -> Options).
+    Returns (models (P,17), list of Stats, list of 3 inlier index arrays per pair)."""
+    lib = lib or load_library()
+    n = len(pairs)
+    arr = (Pair * n)(*pairs)
+    dev = (C.c_int * len(devices))(*devices)
+    models = np.empty((n, MODEL_DOUBLES)); stats = (Stats * n)()
+    tot = sum(p.n for p in pairs)
+    inl = np.zeros(3 * tot + 1, np.int32)
+    if kinds is None:
+        rc = lib.mp_estimate_batch_multi(len(devices), dev, kind, n, arr, C.byref(opt), C.byref(cfg), models.ctypes.data_as(C.c_void_p),
+                                         stats, inl.ctypes.data_as(C.c_void_p))
+    else:
+        ks = (C.c_int * n)(*kinds)
+        ob = (Options * 4)()
+        for k, o in opt_by_kind.items():
+            ob[k] = o
+        rc = lib.mp_estimate_mixed_multi(len(devices), dev, n, ks, arr, ob, C.byref(cfg), models.ctypes.data_as(C.c_void_p),
+                                         stats, inl.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise RuntimeError(f"madpose_b200 error {rc}: {lib.mp_last_error().decode()}")
+    out, o = [], 0
+    for p, s in zip(pairs, stats):
+        out.append([inl[o + t * p.n: o + t * p.n + s.num_inliers[t]].copy() for t in range(3)])
+        o += 3 * p.n
+    return models, list(stats), out
 
 
 class Context:

@@ -148,7 +148,7 @@ mp_config to_c(const EstimatorConfig &e) {
 struct PairIn { darray x0, x1, d0, d1, min_depth, A, B; }; // A,B = K0,K1 (3x3) or pp0,pp1 (2)
 
 void run_batch(int kind, std::vector<PairIn> &in, const HybridLORansacOptions &options, const EstimatorConfig &cfg,
-               std::vector<mp_model> *models, std::vector<HybridRansacStatistics> *stats) {
+               std::vector<mp_model> *models, std::vector<HybridRansacStatistics> *stats, const std::vector<int> &devices = {}) {
     const int P = (int)in.size();
     std::vector<mp_pair> pairs(P);
     size_t total = 0;
@@ -182,8 +182,12 @@ void run_batch(int kind, std::vector<PairIn> &in, const HybridLORansacOptions &o
     std::string err;
     {
         py::gil_scoped_release nogil; // the reference holds the GIL for the whole call; nothing here touches Python
-        std::lock_guard<std::mutex> lock(g_mu);
-        rc = mp_estimate_batch(context(), kind, P, pairs.data(), &o, &e, models->data(), st.data(), inl.data());
+        if (devices.size() > 1) { // the batch is sharded over several GPUs inside the library (no inter-GPU traffic)
+            rc = mp_estimate_batch_multi((int)devices.size(), devices.data(), kind, P, pairs.data(), &o, &e, models->data(), st.data(), inl.data());
+        } else {
+            std::lock_guard<std::mutex> lock(g_mu);
+            rc = mp_estimate_batch(context(), kind, P, pairs.data(), &o, &e, models->data(), st.data(), inl.data());
+        }
         if (rc != MP_OK) err = mp_last_error();
     }
     if (rc == MP_ERR_ARG) throw std::invalid_argument("madpose_b200: " + err);
@@ -294,7 +298,7 @@ std::vector<std::pair<M, HybridRansacStatistics>> estimate_many(std::vector<darr
                                                                 std::vector<darray> d0, std::vector<darray> d1,
                                                                 std::vector<darray> min_depth, std::vector<darray> A,
                                                                 std::vector<darray> B, const HybridLORansacOptions &options,
-                                                                const EstimatorConfig &cfg) {
+                                                                const EstimatorConfig &cfg, const std::vector<int> &devices = {}) {
     const size_t P = x0.size();
     if (x1.size() != P || d0.size() != P || d1.size() != P || min_depth.size() != P || A.size() != P || B.size() != P)
         throw std::invalid_argument("all per-pair lists must have the same length");
@@ -302,7 +306,7 @@ std::vector<std::pair<M, HybridRansacStatistics>> estimate_many(std::vector<darr
     for (size_t p = 0; p < P; p++) in[p] = PairIn{x0[p], x1[p], d0[p], d1[p], min_depth[p], A[p], B[p]};
     std::vector<mp_model> models;
     std::vector<HybridRansacStatistics> stats;
-    run_batch(KIND, in, options, cfg, &models, &stats);
+    run_batch(KIND, in, options, cfg, &models, &stats, devices);
     std::vector<std::pair<M, HybridRansacStatistics>> out;
     for (size_t p = 0; p < P; p++) out.push_back({to_py<M>(KIND, models[p]), stats[p]});
     return out;
@@ -317,9 +321,9 @@ std::vector<std::pair<PoseAndScale, HybridRansacStatistics>> estimate_scale_only
                                                                                       std::vector<darray> d0, std::vector<darray> d1,
                                                                                       std::vector<darray> K0, std::vector<darray> K1,
                                                                                       const HybridLORansacOptions &options,
-                                                                                      const EstimatorConfig &cfg) {
+                                                                                      const EstimatorConfig &cfg, const std::vector<int> &devices = {}) {
     std::vector<darray> md(x0.size());
-    return estimate_many<PoseAndScale, MP_KIND_SCALE_ONLY>(x0, x1, d0, d1, md, K0, K1, options, cfg);
+    return estimate_many<PoseAndScale, MP_KIND_SCALE_ONLY>(x0, x1, d0, d1, md, K0, K1, options, cfg, devices);
 }
 
 template <class M> void bind_pose_common(py::class_<M> &c) {
@@ -442,15 +446,18 @@ PYBIND11_MODULE(_madpose, m) {
           "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig());
     // batch superset (one call, many pairs: what the GPU is for); arguments are lists of the per-pair arrays
     m.def("HybridEstimatePoseScaleOffsetBatch", &estimate_many<PoseScaleOffset, MP_KIND_CALIBRATED>, "x0"_a, "x1"_a, "depth0"_a,
-          "depth1"_a, "min_depth"_a, "K0"_a, "K1"_a, "options"_a, "est_config"_a = EstimatorConfig());
+          "depth1"_a, "min_depth"_a, "K0"_a, "K1"_a, "options"_a, "est_config"_a = EstimatorConfig(), "devices"_a = std::vector<int>());
     m.def("HybridEstimatePoseScaleOffsetSharedFocalBatch", &estimate_many<PoseScaleOffsetSharedFocal, MP_KIND_SHARED_FOCAL>,
-          "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig());
+          "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig(),
+          "devices"_a = std::vector<int>());
     m.def("HybridEstimatePoseScaleOffsetTwoFocalBatch", &estimate_many<PoseScaleOffsetTwoFocal, MP_KIND_TWO_FOCAL>, "x0"_a,
-          "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig());
+          "x1"_a, "depth0"_a, "depth1"_a, "min_depth"_a, "pp0"_a, "pp1"_a, "options"_a, "est_config"_a = EstimatorConfig(),
+          "devices"_a = std::vector<int>());
     m.def("HybridEstimatePoseAndScale", &estimate_scale_only, "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "K0"_a, "K1"_a, "options"_a,
           "est_config"_a = EstimatorConfig());
     m.def("HybridEstimatePoseAndScaleBatch", &estimate_scale_only_many, "x0"_a, "x1"_a, "depth0"_a, "depth1"_a, "K0"_a, "K1"_a,
-          "options"_a, "est_config"_a = EstimatorConfig());
+          "options"_a, "est_config"_a = EstimatorConfig(), "devices"_a = std::vector<int>());
+    m.def("device_count", &mp_device_count, "CUDA devices visible to the process");
     m.def("estimate_scale_and_pose", &scale_and_pose, "X"_a, "Y"_a, "W"_a);
     m.def("solve_scale_and_shift", &solve_raw<MP_KIND_CALIBRATED>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);
     m.def("solve_scale_and_shift_shared_focal", &solve_raw<MP_KIND_SHARED_FOCAL>, "x_homo"_a, "y_homo"_a, "depth_x"_a, "depth_y"_a);

@@ -258,8 +258,9 @@ cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int firs
     if (warp6) { // grid-stride over the list: enough CTAs to fill the machine, no more than the list can use
         const long long want = (ib + W6B_WARPS - 1) / W6B_WARPS;
         const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count));
-        static const cudaError_t attr = cudaFuncSetAttribute(minimal6_warp_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                             (int)(W6B_WARPS * sizeof(Warp6Work)));
+        // (function attributes are per device: set on every launch, the call is cheap)
+        const cudaError_t attr = cudaFuncSetAttribute(minimal6_warp_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                      (int)(W6B_WARPS * sizeof(Warp6Work)));
         if (attr != cudaSuccess) return attr;
         minimal6_warp_batch_kernel<<<grid, W6B_WARPS * 32, W6B_WARPS * sizeof(Warp6Work), s>>>(L, dprm, first, count);
     }
