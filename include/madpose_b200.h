@@ -43,8 +43,8 @@ typedef struct mp_options {
     int32_t non_min_sample_multiplier;      /* 3  */
     uint32_t lo_starting_iterations;        /* 50 */
     int32_t final_least_squares;            /* 0  */
-    int32_t use_ours;                       /* 0 (alternative solvers: not implemented, must be 0) */
-    int32_t use_4p4d;                       /* 0 (must be 0) */
+    int32_t use_ours;                       /* 0; 1: the alternative depth-aware minimal solvers (solver.cpp:536-680,818-984,1045-1153) */
+    int32_t use_4p4d;                       /* 0; 1: two-focal estimator only, the 4p4d solver (solver.cpp:1287-1406); use_ours wins */
 } mp_options;
 
 /* madpose.EstimatorConfig (src/estimator_config.h:5-33) */

@@ -36,7 +36,6 @@ __global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp
 
 static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
                         mp_stats *out_stats, int32_t *out_inliers, bool record_start) {
-    if (opt->use_ours || opt->use_4p4d) return fail(MP_ERR_ARG, "use_ours / use_4p4d solvers are not implemented");
     if (opt->num_lsq_iterations < 0 || opt->num_lo_steps < 0 || opt->min_sample_multiplicator < 0)
         return fail(MP_ERR_ARG, "negative LO option");
     if (c->resident_pairs <= 0) return fail(MP_ERR_ARG, "no resident batch: call mp_upload_batch first");

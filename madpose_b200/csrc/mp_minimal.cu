@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
     const int solver = W.solver[b];
     // point-only solver: candidates only; their tail (triangulation, depth fits) runs in minimal_tail_kernel with one
     // thread per candidate, so that it does not serialise over lanes holding different numbers of candidates
-    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], minimal_flags(prm.cfg), tmp, solver == 0);
+    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], minimal_flags(prm.cfg, prm.opt), tmp, solver == 0);
     W.count[b] = c;
     Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
     HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_tail_kernel(LoopBuffe
     const PairWork &W = L.wk[p];
     Model *slot = L.models + ((size_t)p * LP_BMAX + b) * LP_MM + j;
     Model m = *slot;
-    const bool ok = minimal_tail_ni(pc, L.M + pc.off, W.idx[b], minimal_flags(prm.cfg), &m);
+    const bool ok = minimal_tail_ni(pc, L.M + pc.off, W.idx[b], minimal_flags(prm.cfg, prm.opt), &m);
     if (ok) *slot = m;
     L.cand_ok[((size_t)p * LP_BMAX + b) * LP_MM + j] = ok ? 1 : 0;
 }
@@ -300,11 +300,11 @@ int mp_minimal_solve_batch(mp_ctx *c, int kind, int solver_idx, const mp_pair *p
         MP_CUDA(c->d_work.reserve((size_t)n_samples * kMaxModelsAny * sizeof(Model)));
         const unsigned grid = (unsigned)std::max(1, std::min((n_samples + W6_WARPS - 1) / W6_WARPS, c->sm_count * 8));
         minimal6_warp_kernel<<<grid, W6_WARPS * 32, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), n_samples,
-                                                             c->d_idx.as<int>(), minimal_flags(*cfg), mm, c->d_models.as<Model>(),
+                                                             c->d_idx.as<int>(), minimal_flags(*cfg, *opt), mm, c->d_models.as<Model>(),
                                                              c->d_misc.as<int>(), c->d_work.as<Model>());
     } else
     minimal_kernel<<<(n_samples + 63) / 64, 64, 0, s>>>(c->d_pc.as<PairConst>(), c->d_m64.as<Match64>(), solver_idx, k,
-                                                        n_samples, c->d_idx.as<int>(), minimal_flags(*cfg), mm,
+                                                        n_samples, c->d_idx.as<int>(), minimal_flags(*cfg, *opt), mm,
                                                         c->d_models.as<Model>(), c->d_misc.as<int>());
     MP_CUDA(cudaGetLastError());
     MP_CUDA(cudaEventRecord(c->ev[1], s));

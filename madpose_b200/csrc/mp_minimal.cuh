@@ -7,14 +7,17 @@
 #pragma once
 #include "mp_affine.cuh"
 #include "mp_relpose.cuh"
+#include "mp_alt.cuh"
 
 namespace mp {
 
 // flags of the minimal solvers: EstimatorConfig::min_depth_constraint; EstimatorConfig::use_shift == false
 // (honoured by the calibrated estimator only, hybrid_pose_estimator.cpp:73,146)
-enum { MF_MIN_DEPTH = 1u, MF_NO_SHIFT = 2u };
-MP_HD unsigned minimal_flags(const mp_config &cfg) {
-    return (cfg.min_depth_constraint ? MF_MIN_DEPTH : 0u) | (cfg.use_shift ? 0u : MF_NO_SHIFT);
+// HybridLORansacOptions::use_ours / use_4p4d: the alternative depth-aware solvers of mp_alt.cuh
+enum { MF_MIN_DEPTH = 1u, MF_NO_SHIFT = 2u, MF_OURS = 4u, MF_4P4D = 8u };
+MP_HD unsigned minimal_flags(const mp_config &cfg, const mp_options &opt) {
+    return (cfg.min_depth_constraint ? MF_MIN_DEPTH : 0u) | (cfg.use_shift ? 0u : MF_NO_SHIFT) | (opt.use_ours ? MF_OURS : 0u) |
+           (opt.use_4p4d ? MF_4P4D : 0u);
 }
 
 // calibrated estimator without the shift (EstimatorConfig::use_shift = false, hybrid_pose_estimator.cpp:87-120): scale
@@ -112,7 +115,13 @@ template <int KIND> MP_HD int minimal_affine(const PairConst &pc, const Match64 
         else { x0[k][0] = m.x0x; x0[k][1] = m.x0y; x0[k][2] = 1.0; x1[k][0] = m.x1x; x1[k][1] = m.x1y; x1[k][2] = 1.0; }
         d0[k] = m.d0; d1[k] = m.d1;
     }
-    const int nm = affine_pose_models<KIND>(x0, x1, d0, d1, out);
+    int nm;
+    if ((mflags & MF_OURS) || (KIND == TWO && (mflags & MF_4P4D))) { // use_ours wins over use_4p4d (...two_focal....cpp:87-93)
+        if (KIND == CALIB) nm = alt_calibrated_ours(x0, x1, d0, d1, out);
+        else if (KIND == SHARED) nm = alt_shared_focal_ours(x0, x1, d0, d1, out);
+        else if (mflags & MF_OURS) nm = alt_two_focal_ours(x0, x1, d0, d1, out);
+        else nm = alt_two_focal_4p4d(x0, x1, d0, d1, out);
+    } else nm = affine_pose_models<KIND>(x0, x1, d0, d1, out);
     // the estimator's min-depth filter and offset1 conversion (hybrid_pose_estimator.cpp:79-85 and the focal twins)
     int n = 0;
     for (int q = 0; q < nm; q++) {

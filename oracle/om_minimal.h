@@ -7,6 +7,7 @@
 #pragma once
 #include "om_affine.h"
 #include "om_relpose.h"
+#include "om_alt.h"
 
 namespace om {
 
@@ -55,6 +56,19 @@ inline void minimal_affine(const Problem &P, const int *idx, std::vector<Model> 
         kabsch(3, p0, Y, m.R, m.t);
         m.scale = scale;
         if (model_finite(m)) models->push_back(m);
+        return;
+    }
+    if (P.opt.use_ours || (P.kind == TWO && P.opt.use_4p4d)) { // alternative solvers (om_alt.h); use_ours wins over use_4p4d
+        std::vector<Model> alt;
+        if (P.kind == CALIB) { double a[3][3], b[3][3]; std::memcpy(a, x0, sizeof(a)); std::memcpy(b, x1, sizeof(b)); solve_pose_ours_calibrated(a, b, d0, d1, &alt); }
+        else if (P.kind == SHARED) solve_pose_ours_shared_focal(x0, x1, d0, d1, &alt);
+        else if (P.opt.use_ours) solve_pose_ours_two_focal(x0, x1, d0, d1, &alt);
+        else solve_pose_4p4d_two_focal(x0, x1, d0, d1, &alt);
+        for (Model m : alt) { // the estimator's filter and offset1 conversion, as for the default solver
+            if (P.cfg.min_depth_constraint && !(m.o0 > -P.min_depth[0] && m.o1 > -P.min_depth[1] * m.scale)) continue;
+            m.o1 /= m.scale;
+            if (model_finite(m)) models->push_back(m);
+        }
         return;
     }
     std::vector<AffineSol> sols;

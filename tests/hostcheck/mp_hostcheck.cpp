@@ -53,7 +53,7 @@ int hc_minimal_solve(int kind, const mp_pair *pair, const mp_options *opt, const
     const int k = solver_idx == 0 ? (kind == CALIB ? 3 : 4) : (kind == CALIB ? 5 : (kind == SHARED ? 6 : 7));
     Model tmp[kMaxModelsAny];
     for (int s = 0; s < n_samples; s++) {
-        int c = minimal_solver(hp.pc, hp.M.data(), solver_idx, idx + (size_t)s * k, minimal_flags(*cfg), tmp);
+        int c = minimal_solver(hp.pc, hp.M.data(), solver_idx, idx + (size_t)s * k, minimal_flags(*cfg, *opt), tmp);
         if (c > max_models) c = max_models;
         out_counts[s] = c;
         for (int j = 0; j < c; j++) std::memcpy(out_models + (size_t)s * max_models + j, &tmp[j], sizeof(mp_model));

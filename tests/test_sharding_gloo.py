@@ -17,9 +17,12 @@ WORKER = textwrap.dedent("""
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
     P = 5
-    kind, pairs, opt, cfg, keep = bench.make_batch(P, rank * P)          # rank r owns pairs [r*P, (r+1)*P)
-    first = synth.make_pair(bench.CONFIG, rank * P)
+    (kind, pairs, opt, cfg, keep), = bench.build_workload(1, P, rank, world)   # weak: rank r owns pairs [r*P, (r+1)*P)
+    first = synth.make_pair(1, rank * P)
     assert np.array_equal(keep[0][0]["x0"], first["x0"]) and kind == 1
+    # strong (configs[4]): the fixed batch of 12 mixed pairs is dealt round-robin over the ranks, kinds grouped per rank
+    parts = bench.build_workload(4, 12, rank, world)
+    assert sum(len(part[1]) for part in parts) == 6 and sorted(part[0] for part in parts) == [0, 1, 2]
     sig = torch.tensor([float(sum(p.n for p in pairs))], dtype=torch.float64)
     gathered = [torch.zeros(1, dtype=torch.float64) for _ in range(world)]
     dist.all_gather(gathered, sig)
