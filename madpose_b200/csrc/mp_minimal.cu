@@ -170,31 +170,38 @@ __global__ void __launch_bounds__(W6B_WARPS * 32, 1) minimal6_warp_batch_kernel(
     }
 }
 
-// ---- K1/K2 over all samples of the round: one thread per sample, taken from the two per-solver lists the
-// sample kernel filled (solver 0 first, solver 1 from the next multiple of 32: a warp runs one solver only)
+// ---- K1/K2 over the samples of the round, one thread per sample, ONE kernel per (estimator kind, solver): each launch
+// carries only its own solver's code (all six in one kernel were 113 k instructions = 1.8 MB, thrashing the
+// instruction cache, and every thread reserved the largest solver's 18 KB stack frame).  The samples come from the
+// per-solver lists the sample kernel filled.
+template <int KIND, int SOLVER>
 __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const LoopParams &prm = *prmp;
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     const int grp = first / L.gsz;
-    const int n0 = L.n_items[2 * grp], n1 = L.n_items[2 * grp + 1], n0p = (n0 + 31) & ~31;
-    int item;
-    if (g < n0) item = L.items[(size_t)first * LP_BMAX + g];
-    else if (g >= n0p && g < n0p + n1) item = L.items[(size_t)(L.n_pairs + first) * LP_BMAX + (g - n0p)];
-    else return;
+    if (g >= L.n_items[2 * grp + SOLVER]) return;
+    const int item = L.items[(size_t)(SOLVER * L.n_pairs + first) * LP_BMAX + g];
     const int p = first + item / LP_BMAX, b = item % LP_BMAX;
     PairWork &W = L.wk[p];
     const PairConst &pc = L.pc[p];
-    Model tmp[LP_MM];
-    const int solver = W.solver[b];
-    // point-only solver: candidates only; their tail (triangulation, depth fits) runs in minimal_tail_kernel with one
-    // thread per candidate, so that it does not serialise over lanes holding different numbers of candidates
-    const int c = minimal_solver_ni(pc, L.M + pc.off, solver, W.idx[b], minimal_flags(prm.cfg, prm.opt), tmp, solver == 0);
-    W.count[b] = c;
+    constexpr int MM = SOLVER == 0 ? kMaxModelsAffine[KIND] : kMaxModelsPoints[KIND];
+    Model tmp[MM];
+    const unsigned mflags = minimal_flags(prm.cfg, prm.opt);
     Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
-    HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
-    if (solver == 0) {
-        for (int j = 0; j < c; j++) { out[j] = tmp[j]; pack_hyp(pc.kind, tmp[j], hy + j); }
+    if (SOLVER == 0) {
+        const int c = minimal_affine<KIND>(pc, L.M + pc.off, W.idx[b], mflags, tmp);
+        W.count[b] = c;
+        HypF *hy = L.hyps + ((size_t)p * LP_BMAX + b) * LP_MM;
+        for (int j = 0; j < c; j++) { out[j] = tmp[j]; pack_hyp(KIND, tmp[j], hy + j); }
     } else {
+        // point-only solver: candidates only; their tail (triangulation, depth fits) runs in minimal_tail_kernel with one
+        // thread per candidate, so that it does not serialise over lanes holding different numbers of candidates
+        // (the 6-point solver goes through the noinline entry: inlined into this kernel under the 80-register cap it lost
+        // candidates on the GPU -- test_minimal_modes_whole_path[1] -- while the same source agrees with the oracle in
+        // the stand-alone kernel and in the host build; not root-caused, the thread form is the non-default mode)
+        const int c = KIND == SHARED ? minimal_solver_ni(pc, L.M + pc.off, 1, W.idx[b], mflags, tmp, false)
+                                     : minimal_points<KIND>(pc, L.M + pc.off, W.idx[b], mflags, tmp, false);
+        W.count[b] = c;
         for (int j = 0; j < c; j++) out[j] = tmp[j];
         if (c > 0) {
             const int base = atomicAdd(L.n_cand + grp, c);
@@ -254,7 +261,17 @@ cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int firs
                                  int sm_count, int warp_solvers, cudaStream_t s) {
     const long long ib = items_bound > 0 ? items_bound : 1;
     const int warp6 = (kind == SHARED && warp_solvers) ? 1 : 0; // lists routed to it are empty otherwise
-    minimal_batch_kernel<<<(unsigned)((ib + 32 + 63) / 64), 64, 0, s>>>(L, dprm, first, count);
+    const unsigned grid1 = (unsigned)((ib + 63) / 64);
+    if (kind == CALIB) {
+        minimal_batch_kernel<CALIB, 0><<<grid1, 64, 0, s>>>(L, dprm, first, count);
+        minimal_batch_kernel<CALIB, 1><<<grid1, 64, 0, s>>>(L, dprm, first, count);
+    } else if (kind == SHARED) {
+        minimal_batch_kernel<SHARED, 0><<<grid1, 64, 0, s>>>(L, dprm, first, count);
+        minimal_batch_kernel<SHARED, 1><<<grid1, 64, 0, s>>>(L, dprm, first, count); // list 1 is empty when every sample takes the warp form
+    } else {
+        minimal_batch_kernel<TWO, 0><<<grid1, 64, 0, s>>>(L, dprm, first, count);
+        minimal_batch_kernel<TWO, 1><<<grid1, 64, 0, s>>>(L, dprm, first, count);
+    }
     if (warp6) { // grid-stride over the list: enough CTAs to fill the machine, no more than the list can use
         const long long want = (ib + W6B_WARPS - 1) / W6B_WARPS;
         const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count));

@@ -17,12 +17,13 @@ from tests.test_estimate_gpu import _cnt3, _parse_device_trace, _parse_oracle_tr
 def main():
     config, p = int(sys.argv[1]), int(sys.argv[2])
     ctxn = int(sys.argv[3]) if len(sys.argv) > 3 else 6
-    d, pair, opt, cfg, keep = problem(config, p=p)
+    d, pair, opt, cfg, keep = problem(config, p=p, n=int(os.environ["MP_N"]) if "MP_N" in os.environ else None)
     kind = d["kind"]
     ora = oracle_lib.load(build=False)
     _, so, _, tr = ora.estimate_batch(kind, [pair], opt, cfg, trace_cap=1 << 22)
     eo = [e for e in _parse_oracle_trace(tr)]
     ctx = capi.Context(0)
+    ctx.set_minimal_mode(int(os.environ.get("MP_MIN_MODE", "0")))
     ctx.set_trace(1 << 17)
     _, sg, _ = ctx.estimate_batch(kind, [pair], opt, cfg)
     raw, n = ctx.read_trace(0, cap=1 << 17)
