@@ -2,7 +2,7 @@
 // Same state (an LmDriver in shared memory) and the same algorithm as the scalar driver; what
 // changes is who does it and the form of the elimination: the 11 x 11 systems are spread over
 // the lanes (lane = row), the damped normal equations are factored as L D L^T (right-looking,
-// rows in registers, pivot column broadcast by shuffles: no square roots, one reciprocal per
+// rows in the driver's shared-memory workspace, pivot column broadcast by shuffles: no square roots, one reciprocal per
 // pivot, substitutions without divisions) and the model cost change uses A y = -g - D y.  The
 // scalar driver (L L^T, mp_lm2.cuh) is what the host check compiles against the oracle; the two
 // agree to rounding (the GPU LM tests hold both to the oracle within 1e-8).  Scalar decisions are
@@ -67,7 +67,7 @@ __device__ __forceinline__ double warp_grad_max(const LmSetup &L, const double *
 // LmDriver::first
 #define LMW_T0() long long lmw_t_ = clock64()
 #define LMW_T(slot_) do { if (lane == 0) { const long long n_ = clock64(); d.prof[slot_] += (unsigned long long)(n_ - lmw_t_); lmw_t_ = n_; } } while (0)
-__device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
+static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
     LMW_T0();
     const int nt = L.nt;
@@ -95,12 +95,16 @@ __device__ inline bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     return go != 0;
 }
 
-// LmDriver::propose.  NT > 0: the number of active tangent slots is known at compile time (every slot of the
-// kind is active -- the normal case), the elimination is straight-line code; NT == 0: run-time nt.
-template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane) {
+// LmDriver::propose.  Compact form: ROLLED loops over a working matrix in shared memory (d.Lc, lane = row), one copy
+// of the code for every number of active slots.  The first warp form kept the rows in registers, which needs the
+// elimination fully unrolled: with two instantiations (compile-time / run-time nt) at two call sites block_lm was
+// 17 040 instructions = 272 KB of straight-line code that ONE warp walks once per LM iteration, and lo_kernel 609 KB:
+// the instruction cache thrashed for every phase of the kernel (profiles/r2_whole_path.md).  The arithmetic (operands,
+// order, fused multiply-adds) is the register form's.
+static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
     const LmSetup &L = *d.L;
-    const int nt = NT > 0 ? NT : L.nt;
-#define LMW_IN(k_) (NT > 0 ? (k_) < NT : (k_) < nt)
+    const int nt = L.nt;
+    double *M = d.Lc;
     while (true) {
         int stop = 0;
         if (lane == 0) {
@@ -116,106 +120,73 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
         LMW_T0();
         const double radius = d.radius;
         const bool rowl = lane < nt;
-        const int rl = rowl ? lane : 0; // idle lanes shadow row 0 (their results are never read)
-        // my row of the scaled system; the damped copy stays in registers
-        double row[LM_NT];
-        const double sa = d.scale[rl];
-#pragma unroll
-        for (int b = 0; b < LM_NT; b++) {
-            double v = 0.0;
-            if (LMW_IN(b)) {
-                v = d.A[rl * nt + b] * sa * d.scale[b];
-                if (rowl) d.As[rl * nt + b] = v;
-            }
-            row[b] = v;
-        }
-        const double gsl = d.g[rl] * sa;
-        if (rowl) d.gs[rl] = gsl;
-        {
-            double diag = 0.0;
-#pragma unroll
-            for (int b = 0; b < LM_NT; b++)
-                if (b == rl) diag = row[b];
+        double *row = M + (rowl ? lane : 0) * nt; // idle lanes never store
+        // my row of the scaled, damped system
+        double gsl = 0.0;
+        if (rowl) {
+            const double sa = d.scale[lane];
+            const double *arow = d.A + lane * nt;
+#pragma unroll 2
+            for (int b = 0; b < nt; b++) row[b] = arow[b] * sa * d.scale[b];
+            const double diag = row[lane];
             const double add = fmin(fmax(diag, 1e-6), 1e32) / radius;
-#pragma unroll
-            for (int b = 0; b < LM_NT; b++)
-                if (b == rl) row[b] += add;
-            if (rowl) d.Ad[lane] = add; // the damping D_aa, for the model cost change below
+            row[lane] = diag + add;
+            d.Ad[lane] = add; // the damping D_aa, for the model cost change below
+            gsl = d.g[lane] * sa;
+            d.gs[lane] = gsl;
         }
         __syncwarp();
         LMW_T(1);
         // right-looking LDL^T, no square roots and ONE division per pivot (the reciprocal, computed by every lane):
-        // after step k, row[k] = l_ik on lanes i > k; pivots d_k > 0 <=> the scalar driver's Cholesky succeeds.
+        // after step k, M[i][k] = l_ik for i > k; pivots d_k > 0 <=> the scalar driver's Cholesky succeeds.
         // (The scalar driver of mp_lm2.cuh uses L L^T; the two agree to rounding, ~1e-16 relative in the step.)
         bool bad = false;
-        double rinv[LM_NT];
-#pragma unroll
-        for (int k = 0; k < LM_NT; k++) {
-            rinv[k] = 0.0;
-            if (LMW_IN(k)) {
-                const double dk = __shfl_sync(LMW_FULL, row[k], k);
-                bad = bad || !(dk > 0.0) || !finite_d(dk);
-                const double rk = 1.0 / dk;
-                rinv[k] = rk;
-                const double aik = row[k], lik = aik * rk; // a_ik = l_ik d_k
-                if (lane != k) row[k] = lik;
-#pragma unroll
-                for (int j = k + 1; j < LM_NT; j++) {
-                    if (LMW_IN(j)) {
-                        const double ajk = __shfl_sync(LMW_FULL, aik, j);
-                        if (j <= lane) row[j] -= lik * ajk; // a_ij -= l_ik d_k l_jk
-                    }
-                }
+        for (int k = 0; k < nt; k++) {
+            const double dk = M[k * nt + k];
+            bad = bad || !(dk > 0.0) || !finite_d(dk);
+            const double rk = 1.0 / dk;
+            const double aik = row[k], lik = aik * rk; // a_ik = l_ik d_k
+            if (lane == k) d.wr[k] = rk;
+#pragma unroll 2
+            for (int j = k + 1; j < nt; j++) {
+                const double ajk = __shfl_sync(LMW_FULL, aik, j);
+                if (rowl && j <= lane) row[j] -= lik * ajk; // a_ij -= l_ik d_k l_jk
             }
-        }
-        if (rowl) {
-#pragma unroll
-            for (int j = 0; j < LM_NT; j++)
-                if (j < lane) d.Lc[lane * nt + j] = row[j]; // strictly lower part: the unit-triangular factor
+            if (rowl && lane > k) row[k] = lik;
+            __syncwarp();
         }
         LMW_T(2);
         // forward substitution with the unit lower factor (column-oriented), then the diagonal
         {
             double s = gsl;
-#pragma unroll
-            for (int k = 0; k < LM_NT; k++) {
-                if (LMW_IN(k)) {
-                    const double yk = __shfl_sync(LMW_FULL, s, k);
-                    if (lane == k) d.yw[k] = yk * rinv[k];
-                    if (lane > k) s -= row[k] * yk;
-                }
+            for (int k = 0; k < nt; k++) {
+                const double yk = __shfl_sync(LMW_FULL, s, k);
+                if (lane == k) d.yw[k] = yk * d.wr[k];
+                if (rowl && lane > k) s -= row[k] * yk;
             }
         }
         __syncwarp();
         LMW_T(3);
-        // back substitution with the unit upper factor (every lane, redundantly): FMAs only
-        double xs[LM_NT];
+        // back substitution with the unit upper factor: every lane computes the same values redundantly (FMAs only) and
+        // stores them to the same slots of d.xs -- a lane reads back what it (and every other lane, identically) wrote
         bool ok = !bad;
-#pragma unroll
-        for (int i = LM_NT - 1; i >= 0; i--) {
-            double v = 0.0;
-            if (LMW_IN(i)) {
-                v = d.yw[i];
-#pragma unroll
-                for (int k = i + 1; k < LM_NT; k++)
-                    if (LMW_IN(k)) v -= d.Lc[k * nt + i] * xs[k];
-                ok = ok && finite_d(v);
-            }
-            xs[i] = v;
+        for (int i = nt - 1; i >= 0; i--) {
+            double v = d.yw[i];
+#pragma unroll 2
+            for (int k = i + 1; k < nt; k++) v -= M[k * nt + i] * d.xs[k];
+            ok = ok && finite_d(v);
+            d.xs[i] = v;
         }
+        __syncwarp();
         LMW_T(4);
         // model cost change -(g.y + y.A y / 2) with A y = -g - D y (y solves the damped system): 2 x nt terms
         double mcc = 0;
         if (ok) {
             double dg = 0, dDd = 0;
-#pragma unroll
-            for (int a = 0; a < LM_NT; a++) xs[a] = -xs[a];
-#pragma unroll
-            for (int a = 0; a < LM_NT; a++) {
-                if (LMW_IN(a)) {
-                    dg += xs[a] * d.gs[a];
-                    dDd += xs[a] * xs[a] * d.Ad[a];
-                }
+            for (int a = 0; a < nt; a++) {
+                const double xa = -d.xs[a];
+                dg += xa * d.gs[a];
+                dDd += xa * xa * d.Ad[a];
             }
             mcc = 0.5 * (dDd - dg);
         }
@@ -232,13 +203,7 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
             continue;
         }
         if (lane == 0) { d.mcc = mcc; d.n_invalid = 0; }
-        if (rowl) { // the step in the unscaled tangent space, one entry per lane
-            double mine = 0.0;
-#pragma unroll
-            for (int a = 0; a < LM_NT; a++)
-                if (a == lane) mine = xs[a];
-            d.y[lane] = mine * d.scale[lane];
-        }
+        if (rowl) d.y[lane] = -d.xs[lane] * d.scale[lane]; // the step in the unscaled tangent space, one entry per lane
         __syncwarp();
         const double xcv = warp_plus_component(L, d.x, d.y, 1.0, lane);
         if (lane < LM_NA) d.xc[lane] = xcv;
@@ -246,16 +211,10 @@ template <int NT> __device__ inline bool warp_lm_propose_t(LmDriver &d, int lane
         LMW_T(6);
         return true;
     }
-#undef LMW_IN
-}
-// NTK = number of tangent slots of the estimator kind (9 calibrated, 10 shared focal, 11 two focals)
-template <int NTK> __device__ __forceinline__ bool warp_lm_propose(LmDriver &d, int lane) {
-    if (d.L->nt == NTK) return warp_lm_propose_t<NTK>(d, lane);
-    return warp_lm_propose_t<0>(d, lane);
 }
 
 // LmDriver::feed
-__device__ inline bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
+static __device__ __noinline__ bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
     const int nt = L.nt;
     LMW_T0();

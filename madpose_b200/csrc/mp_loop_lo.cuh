@@ -123,22 +123,18 @@ template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, con
     __syncthreads();
     if (sh->lm_go) {
         const int lane = threadIdx.x & 31;
-        constexpr int NTK = KIND == CALIB ? 9 : (KIND == SHARED ? 10 : 11);
-        ev();
-        if (threadIdx.x < 32) { // warp 0 drives (mp_lm_warp.cuh); the other warps wait at the barrier
-            const bool go = warp_lm_first(drv, sh->total, lane) && warp_lm_propose<NTK>(drv, lane);
-            if (lane == 0) sh->lm_go = go ? 1 : 0;
-            if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
-        }
-        __syncthreads();
-        while (sh->lm_go) {
+        bool first = true;
+        while (true) { // ONE call site for each part of the driver: its code exists once in the kernel
             ev();
-            if (threadIdx.x < 32) {
-                const bool go = warp_lm_feed(drv, sh->total, lane) && warp_lm_propose<NTK>(drv, lane);
+            if (threadIdx.x < 32) { // warp 0 drives (mp_lm_warp.cuh); the other warps wait at the barrier
+                const bool go = (first ? warp_lm_first(drv, sh->total, lane) : warp_lm_feed(drv, sh->total, lane)) &&
+                                warp_lm_propose(drv, lane);
                 if (lane == 0) sh->lm_go = go ? 1 : 0;
                 if (lane < LM_NA) sh->lm_x[lane] = drv.xc[lane];
             }
+            first = false;
             __syncthreads();
+            if (!sh->lm_go) break;
         }
     }
     if (threadIdx.x == 0) {
@@ -385,7 +381,7 @@ __device__ inline double block_score_inliers(const BlockCtx &C, const Model &m, 
 }
 
 // LocalOptimization (hybrid_ransac.h:383-482).  best / best_score / best_solver live in shared memory.
-template <int KIND> __device__ void block_local_optimization(const BlockCtx &C, int solver, Model *best,
+template <int KIND> __device__ __noinline__ void block_local_optimization(const BlockCtx &C, int solver, Model *best,
                                                              double *best_score, int *best_solver) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
