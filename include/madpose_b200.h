@@ -176,6 +176,20 @@ int mp_last_timing(mp_ctx *ctx, double *kernel_ms, double *total_ms, int *launch
  * scores_f32: fused fp32 scoring kernel; scores_f64: exact fp64 evaluation. Either may be NULL. */
 int mp_score_batch(mp_ctx *ctx, int kind, const mp_pair *pair, const mp_options *opt, const mp_config *cfg,
                    int n_models, const mp_model *models, float *scores_f32, double *scores_f64);
+/* The fp64 leg of mp_score_batch WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The scratch the scoring path needs (the pair's constants and fp64 match records) lives in one
+ * fixed file-scope device array of the library (~770 KB per GPU, held until the process exits), so a pair may have at
+ * most MP_NOALLOC_MAX_MATCHES matches: larger pairs are rejected with MP_ERR_ARG (use mp_score_batch).
+ * pair_dev: an mp_pair whose x0, x1, d0, d1 are DEVICE pointers on `device`; d_models (n_models) and d_scores64
+ * (n_models, output) are DEVICE buffers of the caller; stream: a cudaStream_t of `device` (NULL = default stream).
+ * The call only enqueues work on `stream` and returns: synchronise before reading d_scores64.  It calls no
+ * cudaMalloc / cudaFree / allocating routine.  All calls on a device share the scratch array, which keeps the last
+ * call's contents (the call clears and rewrites what it uses): calls that overlap on the GPU race -- keep them on one
+ * stream.  Scores are bit-identical to mp_score_batch's scores_f64. */
+#define MP_NOALLOC_MAX_MATCHES 16384
+int mp_score_models_noalloc(int device, int kind, const mp_pair *pair_dev, const mp_options *opt, const mp_config *cfg,
+                            int n_models, const mp_model *d_models, double *d_scores64, void *stream);
 /* The step before the path: madpose.utils.get_depths (madpose/utils.py:4-22) -- nearest-neighbour
  * lookup of the prior depth of n keypoints in a depth map of another resolution: scale the keypoints by
  * (map_w / img_w, map_h / img_h), round half to even (numpy.round), clip to the map, gather.

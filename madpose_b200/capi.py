@@ -125,6 +125,7 @@ _SYMBOLS = [
     "mp_last_error", "mp_create", "mp_destroy", "mp_device_info", "mp_measure_alu_peaks", "mp_estimate_batch",
     "mp_upload_batch", "mp_estimate_resident", "mp_last_breakdown", "mp_set_groups", "mp_set_batch", "mp_last_phase_cycles", "mp_last_timing", "mp_score_batch", "mp_inliers", "mp_minimal_solve_batch", "mp_lm_batch", "mp_get_depths", "mp_pose_errors",
     "mp_solve_affine", "mp_estimate_scale_and_pose", "mp_set_trace", "mp_read_trace", "mp_set_minimal_mode", "mp_set_warp_from_iteration", "mp_estimate_batch_multi", "mp_estimate_mixed_multi", "mp_device_count",
+    "mp_score_models_noalloc",
 ]
 
 
@@ -140,6 +141,20 @@ def load_library(path=LIB_PATH):
         getattr(lib, s).restype = C.c_int
     lib.mp_destroy.restype = None
     return lib
+
+
+NOALLOC_MAX_MATCHES = 16384  # MP_NOALLOC_MAX_MATCHES (include/madpose_b200.h)
+
+
+def score_models_noalloc(device, kind, pair_dev, opt, cfg, n_models, d_models, d_scores64, stream=0, lib=None):
+    """mp_score_models_noalloc: fp64 scores of n_models models of one pair with NO allocation inside the library.
+    pair_dev: a Pair whose x0/x1/d0/d1 hold DEVICE addresses; d_models / d_scores64: device addresses (ints);
+    stream: a cudaStream_t handle (int).  Only enqueues work: synchronise the stream before reading the scores."""
+    lib = lib or load_library()
+    rc = lib.mp_score_models_noalloc(int(device), int(kind), C.byref(pair_dev), C.byref(opt), C.byref(cfg), int(n_models),
+                                     C.c_void_p(int(d_models)), C.c_void_p(int(d_scores64)), C.c_void_p(int(stream)))
+    if rc != 0:
+        raise RuntimeError(f"mp_score_models_noalloc failed ({rc}): {lib.mp_last_error().decode()}")
 
 
 def estimate_batch_multi(devices, kind, pairs, opt, cfg, lib=None, kinds=None, opt_by_kind=None):
