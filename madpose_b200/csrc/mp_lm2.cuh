@@ -120,7 +120,8 @@ struct LmDriver {
     double A[LM_NT * LM_NT], g[LM_NT], As[LM_NT * LM_NT], gs[LM_NT], scale[LM_NT];
     double Ad[LM_NT * LM_NT], Lc[LM_NT * LM_NT], An[LM_NT * LM_NT], gn[LM_NT], y[LM_NT], yw[LM_NT]; // workspace (kept
     // in the object so that a driver placed in shared memory does all its array work there)
-    double wr[LM_NT], xs[LM_NT]; // warp driver (mp_lm_warp.cuh): reciprocals of the L D L^T pivots, scaled solution
+    double wr[LM_NT];      // warp driver (mp_lm_warp.cuh): reciprocals of the L D L^T pivots
+    short cpos[LM_NT * (LM_NT + 1) / 2], cposT[LM_NT * (LM_NT + 1) / 2]; // warp driver: slot -> compact position
     double cost, radius, decrease, mcc;
     double min_cost, cur_cost, ref_cost, cand_cost, acc_ref, acc_cand;
     int n_nonmono, n_invalid, it;

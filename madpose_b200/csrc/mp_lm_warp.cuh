@@ -14,16 +14,29 @@ namespace mp {
 constexpr unsigned LMW_FULL = 0xffffffffu;
 constexpr int LM_TRI = LM_NT * (LM_NT + 1) / 2;
 
-// reduced full-slot sums (LmAcc as a flat array) -> compact nt x nt system; = lm_compress
-__device__ __forceinline__ void warp_compress(const LmSetup &L, const double *tot, double *A, double *g, int lane) {
+// reduced full-slot sums (LmAcc as a flat array) -> compact nt x nt system; = lm_compress.  The map from the 66 upper-
+// triangle slots to compact positions depends on the set-up only: warp_lm_first decodes it once per solve into
+// d.cpos / d.cposT, every evaluation after that is a table-driven scatter.
+__device__ __forceinline__ void warp_compress_table(LmDriver &d, int lane) {
+    const LmSetup &L = *d.L;
     const int nt = L.nt;
     for (int k = lane; k < LM_TRI; k += 32) {
         int a = 0, r = k;
         while (r >= LM_NT - a) { r -= LM_NT - a; a++; }
         const int b = a + r, ia = L.slot[a], ib = L.slot[b];
-        if (ia >= 0 && ib >= 0) {
+        const bool on = ia >= 0 && ib >= 0;
+        d.cpos[k] = (short)(on ? ia * nt + ib : -1);
+        d.cposT[k] = (short)(on ? ib * nt + ia : -1);
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void warp_compress(const LmDriver &d, const double *tot, double *A, double *g, int lane) {
+    const LmSetup &L = *d.L;
+    for (int k = lane; k < LM_TRI; k += 32) {
+        const int p = d.cpos[k];
+        if (p >= 0) {
             const double v = tot[k];
-            A[ia * nt + ib] = v; A[ib * nt + ia] = v;
+            A[p] = v; A[d.cposT[k]] = v;
         }
     }
     if (lane < LM_NT && L.slot[lane] >= 0) g[L.slot[lane]] = tot[LM_TRI + lane];
@@ -71,7 +84,8 @@ static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot
     const LmSetup &L = *d.L;
     LMW_T0();
     const int nt = L.nt;
-    warp_compress(L, tot, d.A, d.g, lane);
+    warp_compress_table(d, lane);
+    warp_compress(d, tot, d.A, d.g, lane);
     if (lane < nt) d.scale[lane] = 1.0 / (1.0 + sqrt(d.A[lane * nt + lane]));
     __syncwarp();
     int go = 0;
@@ -95,16 +109,28 @@ static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot
     return go != 0;
 }
 
-// LmDriver::propose.  Compact form: ROLLED loops over a working matrix in shared memory (d.Lc, lane = row), one copy
-// of the code for every number of active slots.  The first warp form kept the rows in registers, which needs the
-// elimination fully unrolled: with two instantiations (compile-time / run-time nt) at two call sites block_lm was
-// 17 040 instructions = 272 KB of straight-line code that ONE warp walks once per LM iteration, and lo_kernel 609 KB:
-// the instruction cache thrashed for every phase of the kernel (profiles/r2_whole_path.md).  The arithmetic (operands,
-// order, fused multiply-adds) is the register form's.
+// LmDriver::propose.  One copy of the code for every number of active slots, working matrices in shared memory at the
+// fixed stride LM_NT (d.Lc: the matrix being eliminated, d.As: the unit-lower factor).  The first warp form kept the
+// rows in registers, fully unrolled, in two instantiations at two call sites: block_lm was 17 040 instructions = 272 KB
+// of straight-line code (lo_kernel 609 KB) and the instruction cache thrashed for every phase of the kernel
+// (profiles/r2_whole_path.md).  A lone warp is latency-bound (~8 cycles per instruction), so what counts here is the
+// length of the dependent chain: the elimination is spread over the ENTRIES of the lower triangle (<= 66 entries, <= 3
+// per lane: one step = load, reciprocal, multiply-add, store for every lane at once) instead of over the rows (a
+// shuffle + read-modify-write loop of up to 10 trips per step).  The arithmetic -- operands, order of the sums, fused
+// multiply-adds -- is the row form's.
 static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
     const LmSetup &L = *d.L;
     const int nt = L.nt;
-    double *M = d.Lc;
+    constexpr int S = LM_NT;
+    double *M = d.Lc, *Lf = d.As;
+    // the lower-triangle entries (i >= j) this lane eliminates: e = i (i + 1) / 2 + j for e = lane, lane + 32, lane + 64
+    int ei[3], ej[3];
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+        const int e = lane + 32 * q;
+        const int i = (int)((sqrtf((float)(8 * e + 1)) - 1.0f) * 0.5f); // exact: 8 e + 1 is a square only at j = 0
+        ei[q] = i; ej[q] = e - i * (i + 1) / 2;
+    }
     while (true) {
         int stop = 0;
         if (lane == 0) {
@@ -120,10 +146,10 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
         LMW_T0();
         const double radius = d.radius;
         const bool rowl = lane < nt;
-        double *row = M + (rowl ? lane : 0) * nt; // idle lanes never store
-        // my row of the scaled, damped system
+        // the scaled, damped system: one row per lane
         double gsl = 0.0;
         if (rowl) {
+            double *row = M + lane * S;
             const double sa = d.scale[lane];
             const double *arow = d.A + lane * nt;
 #pragma unroll 2
@@ -138,21 +164,24 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
         __syncwarp();
         LMW_T(1);
         // right-looking LDL^T, no square roots and ONE division per pivot (the reciprocal, computed by every lane):
-        // after step k, M[i][k] = l_ik for i > k; pivots d_k > 0 <=> the scalar driver's Cholesky succeeds.
-        // (The scalar driver of mp_lm2.cuh uses L L^T; the two agree to rounding, ~1e-16 relative in the step.)
+        // step k takes a_ij -= (a_ik / d_k) a_jk on every entry i >= j > k and leaves l_ik = a_ik / d_k in the factor;
+        // pivots d_k > 0 <=> the scalar driver's Cholesky succeeds.  (The scalar driver of mp_lm2.cuh uses L L^T; the
+        // two agree to rounding, ~1e-16 relative in the step.)  Column k is read-only during step k.
         bool bad = false;
         for (int k = 0; k < nt; k++) {
-            const double dk = M[k * nt + k];
+            const double dk = M[k * S + k];
             bad = bad || !(dk > 0.0) || !finite_d(dk);
             const double rk = 1.0 / dk;
-            const double aik = row[k], lik = aik * rk; // a_ik = l_ik d_k
-            if (lane == k) d.wr[k] = rk;
-#pragma unroll 2
-            for (int j = k + 1; j < nt; j++) {
-                const double ajk = __shfl_sync(LMW_FULL, aik, j);
-                if (rowl && j <= lane) row[j] -= lik * ajk; // a_ij -= l_ik d_k l_jk
+            if (lane == 0) d.wr[k] = rk;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int i = ei[q], j = ej[q];
+                if (i < nt && i > k && j >= k) {
+                    const double lik = M[i * S + k] * rk; // a_ik = l_ik d_k
+                    if (j == k) Lf[i * S + k] = lik;
+                    else M[i * S + j] -= lik * M[j * S + k];
+                }
             }
-            if (rowl && lane > k) row[k] = lik;
             __syncwarp();
         }
         LMW_T(2);
@@ -162,31 +191,39 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
             for (int k = 0; k < nt; k++) {
                 const double yk = __shfl_sync(LMW_FULL, s, k);
                 if (lane == k) d.yw[k] = yk * d.wr[k];
-                if (rowl && lane > k) s -= row[k] * yk;
+                if (rowl && lane > k) s -= Lf[lane * S + k] * yk;
             }
         }
         __syncwarp();
         LMW_T(3);
-        // back substitution with the unit upper factor: every lane computes the same values redundantly (FMAs only) and
-        // stores them to the same slots of d.xs -- a lane reads back what it (and every other lane, identically) wrote
+        // back substitution with the unit upper factor (every lane, redundantly, in registers): FMAs only
+        double xs[LM_NT];
         bool ok = !bad;
-        for (int i = nt - 1; i >= 0; i--) {
-            double v = d.yw[i];
-#pragma unroll 2
-            for (int k = i + 1; k < nt; k++) v -= M[k * nt + i] * d.xs[k];
-            ok = ok && finite_d(v);
-            d.xs[i] = v;
+#pragma unroll
+        for (int i = LM_NT - 1; i >= 0; i--) {
+            double v = 0.0;
+            if (i < nt) {
+                v = d.yw[i];
+#pragma unroll
+                for (int k = i + 1; k < LM_NT; k++)
+                    if (k < nt) v -= Lf[k * S + i] * xs[k];
+                ok = ok && finite_d(v);
+            }
+            xs[i] = v;
         }
-        __syncwarp();
         LMW_T(4);
         // model cost change -(g.y + y.A y / 2) with A y = -g - D y (y solves the damped system): 2 x nt terms
         double mcc = 0;
         if (ok) {
             double dg = 0, dDd = 0;
-            for (int a = 0; a < nt; a++) {
-                const double xa = -d.xs[a];
-                dg += xa * d.gs[a];
-                dDd += xa * xa * d.Ad[a];
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++) xs[a] = -xs[a];
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++) {
+                if (a < nt) {
+                    dg += xs[a] * d.gs[a];
+                    dDd += xs[a] * xs[a] * d.Ad[a];
+                }
             }
             mcc = 0.5 * (dDd - dg);
         }
@@ -203,7 +240,13 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
             continue;
         }
         if (lane == 0) { d.mcc = mcc; d.n_invalid = 0; }
-        if (rowl) d.y[lane] = -d.xs[lane] * d.scale[lane]; // the step in the unscaled tangent space, one entry per lane
+        if (rowl) { // the step in the unscaled tangent space, one entry per lane
+            double mine = 0.0;
+#pragma unroll
+            for (int a = 0; a < LM_NT; a++)
+                if (a == lane) mine = xs[a];
+            d.y[lane] = mine * d.scale[lane];
+        }
         __syncwarp();
         const double xcv = warp_plus_component(L, d.x, d.y, 1.0, lane);
         if (lane < LM_NA) d.xc[lane] = xcv;
@@ -216,9 +259,7 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
 // LmDriver::feed
 static __device__ __noinline__ bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
-    const int nt = L.nt;
     LMW_T0();
-    warp_compress(L, tot, d.An, d.gn, lane);
     int verdict = 0; // 0 finished, 1 rejected step (continue), 2 accepted step
     double cc = 0, rel = 0;
     double sn = 0, xn = 0; // |xc - x|^2 and |x|^2: one component per lane, butterfly sums
@@ -237,10 +278,8 @@ static __device__ __noinline__ bool warp_lm_feed(LmDriver &d, const double *tot,
         }
     }
     verdict = __shfl_sync(LMW_FULL, verdict, 0);
-    if (verdict == 2) {
-        for (int e = lane; e < nt * nt; e += 32) d.A[e] = d.An[e];
-        if (lane < nt) d.g[lane] = d.gn[lane];
-        __syncwarp();
+    if (verdict == 2) { // accepted: the system at xc replaces the current one in place (a rejected one is never needed)
+        warp_compress(d, tot, d.A, d.g, lane);
         if (lane < LM_NA) d.x[lane] = d.xc[lane];
         __syncwarp();
         const double gm = warp_grad_max(L, d.x, d.g, lane);

@@ -1,50 +1,44 @@
 #!/usr/bin/env python
-"""Summarise an .ncu-rep per source line: `python tools/ncu_lines.py report.ncu-rep [top]`.
-Uses `ncu --page source --print-source cuda,sass --csv` (needs -lineinfo and --import-source on)."""
-import collections
-import csv
-import subprocess
-import sys
-
-
-def load(rep):
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv"],
-                         capture_output=True, text=True).stdout
-    cur, hdr, rows = None, None, []
-    for r in csv.reader(out.splitlines()):
-        if len(r) >= 2 and r[0] == "File Path":
-            cur = r[1]
-        elif r and r[0] == "Line No":
-            hdr = r
-        elif hdr and len(r) == len(hdr) and r[0] not in ("", "Line No"):
-            rows.append((cur, r))
-    return hdr, rows
-
-
-def main():
-    rep = sys.argv[1]
-    top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-    hdr, rows = load(rep)
-    ci = {n: i for i, n in enumerate(hdr)}
-    i_s, i_inst, i_thr = ci["# Samples"], ci["Instructions Executed"], ci["Thread Instructions Executed"]
-    tot_s = sum(int(r[i_s]) for _, r in rows) or 1
-    tot_i = sum(int(r[i_inst]) for _, r in rows) or 1
-    per_file = collections.defaultdict(lambda: [0, 0, 0])
-    for f, r in rows:
-        a = per_file[f.split("/")[-1]]
-        a[0] += int(r[i_s]); a[1] += int(r[i_inst]); a[2] += int(r[i_thr])
-    print(f"total samples {tot_s}, warp instructions {tot_i}")
-    print("--- per file: samples share | inst share | threads/inst")
-    for f, a in sorted(per_file.items(), key=lambda x: -x[1][0]):
-        print(f"{f:28s} {a[0] / tot_s:6.3f} {a[1] / tot_i:6.3f} {a[2] / max(a[1], 1):6.1f}")
-    print(f"--- top {top} lines by samples")
-    stall_cols = [n for n in hdr if n.startswith("stall_") and "Not Issued" not in n]
-    for f, r in sorted(rows, key=lambda x: -int(x[1][i_s]))[:top]:
-        st = sorted(((int(r[ci[n]]), n[6:]) for n in stall_cols), reverse=True)[:2]
-        sts = " ".join(f"{n}:{v}" for v, n in st if v)
-        print(f"{int(r[i_s]) / tot_s:6.3f} {int(r[i_inst]) / tot_i:6.3f} thr/inst {int(r[i_thr]) / max(int(r[i_inst]), 1):5.1f} "
-              f"{f.split('/')[-1]}:{r[0]:>4s} [{sts}] {r[1].strip()[:90]}")
-
-
-if __name__ == "__main__":
-    main()
+"""Per-source-line and per-function summary of an `ncu --page source --csv` export (SASS level) of one kernel, joined
+with `nvdisasm -g -c` of the same cubin (the line table).  python tools/ncu_lines.py src.csv disasm.txt kernel_substr"""
+import collections, csv, re, subprocess, sys
+src, dis, kname = sys.argv[1:4]
+lines = open(dis).read().split("\n")
+sec = None; cur = None; func = None; table = []  # per instruction (in order): (file, line, func)
+for l in lines:
+    m = re.match(r"^//-+ \.text\.(\S+)", l)
+    if m: sec = m.group(1); cur = None; func = sec; continue
+    if sec is None or kname not in sec: continue
+    m = re.match(r'\s*//## File "([^"]+)", line (\d+)', l)
+    if m: cur = (m.group(1).split("/")[-1], int(m.group(2))); continue
+    m = re.match(r"^(\S+):\s*$", l)
+    if m and not m.group(1).startswith(".L"): func = m.group(1); continue
+    if re.match(r"\s+/\*[0-9a-f]{4,6}\*/", l): table.append((cur, func))
+rows = list(csv.reader(open(src)))
+hdr = rows[1]; body = rows[2:]
+ci = {h: i for i, h in enumerate(hdr)}
+assert len(body) >= len(table), (len(body), len(table))
+stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
+per_line = collections.defaultdict(lambda: [0, 0, collections.Counter()]); per_func = collections.defaultdict(lambda: [0, 0])
+tot_s = tot_i = 0
+for r, (cl, fn) in zip(body, table):
+    s = int(r[ci["# Samples"]] or 0); n = int(r[ci["Instructions Executed"]] or 0)
+    tot_s += s; tot_i += n
+    e = per_line[cl]; e[0] += s; e[1] += n
+    for h in stall_cols:
+        v = int(r[ci[h]] or 0)
+        if v: e[2][h[6:]] += v
+    f = per_func[fn]; f[0] += s; f[1] += n
+print("total samples", tot_s, "warp instructions", tot_i, "static instructions", len(table))
+def dem(n):
+    n = n.split("$")[-1] if "$" in n else n
+    return subprocess.run(["c++filt", n], capture_output=True, text=True).stdout.strip()[:70]
+print("--- per function: samples share | inst share")
+for fn, (s, n) in sorted(per_func.items(), key=lambda kv: -kv[1][0])[:16]:
+    print(f"{s / tot_s:6.3f} {n / tot_i:6.3f}  {dem(fn)}")
+flt = sys.argv[4] if len(sys.argv) > 4 else None
+print("--- top lines by samples" + (f" in {flt}" if flt else ""))
+items = [(k, v) for k, v in per_line.items() if k and (not flt or k[0] == flt)]
+for (f, ln), (s, n, st) in sorted(items, key=lambda kv: -kv[1][0])[:int(sys.argv[5]) if len(sys.argv) > 5 else 40]:
+    top = " ".join(f"{k}:{v}" for k, v in st.most_common(3))
+    print(f"{s / tot_s:6.3f} {n / tot_i:6.3f} {f}:{ln} [{top}]")
