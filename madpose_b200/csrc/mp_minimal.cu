@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
         // candidates on the GPU -- test_minimal_modes_whole_path[1] -- while the same source agrees with the oracle in
         // the stand-alone kernel and in the host build; not root-caused, the thread form is the non-default mode)
         const int c = KIND == SHARED ? minimal_solver_ni(pc, L.M + pc.off, 1, W.idx[b], mflags, tmp, false)
-                                     : minimal_points<KIND>(pc, L.M + pc.off, W.idx[b], mflags, tmp, false);
+                                     : minimal_points<KIND>(pc, L.M + pc.off, W.idx[b], mflags, tmp, false, KIND == TWO);
         W.count[b] = c;
         for (int j = 0; j < c; j++) out[j] = tmp[j];
         if (c > 0) {
@@ -208,6 +208,41 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
             int *cl = L.cand + (size_t)first * LP_BMAX * LP_MM;
             for (int j = 0; j < c; j++) cl[base + j] = item * LP_MM + j;
         }
+    }
+}
+
+// cv::recoverPose (...two_focal_estimator.cpp:143) for the candidates of the 7-point solver, ONE WARP per candidate:
+// lane = (pose hypothesis c, point i), 28 of 32 lanes triangulate one point each (one thread per sample walked the 84
+// triangulations of its <= 3 candidates in sequence: 32 % of the GPU time of configs[2]).  The candidate arrives with E in
+// Model::R (minimal_points, defer_pose); every lane factors E redundantly, the votes are one ballot.
+__global__ void __launch_bounds__(128) recover_pose_warp_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int grp = first / L.gsz;
+    const int nc = L.n_cand[grp];
+    for (int g = warp; g < nc; g += nwarps) {
+        const int e = L.cand[(size_t)first * LP_BMAX * LP_MM + g];
+        const int item = e / LP_MM, j = e % LP_MM;
+        const int p = first + item / LP_BMAX, b = item % LP_BMAX;
+        const PairConst &pc = L.pc[p];
+        const PairWork &W = L.wk[p];
+        Model *slot = L.models + ((size_t)p * LP_BMAX + b) * LP_MM + j;
+        double E[9], Ra[9], Rb[9], tt[3];
+        for (int k = 0; k < 9; k++) E[k] = slot->R[k];
+        essential_factor(E, Ra, Rb, tt);
+        bool ok = false;
+        if (lane < 28) {
+            const Match64 m = L.M[pc.off + W.idx[b][lane % 7]];
+            const double p0[2] = {m.x0x, m.x0y}, p1[2] = {m.x1x, m.x1y}; // un-calibrated points with K = I, as the reference does
+            ok = recover_pose_point_ok(Ra, Rb, tt, lane / 7, p0, p1, 1e9);
+        }
+        const unsigned votes = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) { // (every lane read E before the ballot)
+            int good[4];
+            for (int c = 0; c < 4; c++) good[c] = __popc((votes >> (7 * c)) & 0x7fu);
+            recover_pose_select(Ra, Rb, tt, good, slot->R, slot->t);
+        }
+        __syncwarp();
     }
 }
 
@@ -281,6 +316,7 @@ cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int firs
         if (attr != cudaSuccess) return attr;
         minimal6_warp_batch_kernel<<<grid, W6B_WARPS * 32, W6B_WARPS * sizeof(Warp6Work), s>>>(L, dprm, first, count);
     }
+    if (kind == TWO) recover_pose_warp_kernel<<<(unsigned)std::max<long long>(1, std::min<long long>((ib * 3 + 3) / 4, 8ll * sm_count)), 128, 0, s>>>(L, dprm, first, count);
     // worst case of the candidate list: every sample of the round is a point-solver sample with LP_MM candidates; the
     // threads beyond the actual count exit at once
     minimal_tail_kernel<<<(unsigned)((ib * LP_MM + 63) / 64), 64, 0, s>>>(L, dprm, first, count);

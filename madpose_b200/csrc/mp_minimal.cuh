@@ -207,8 +207,10 @@ template <int KIND, int NPT> MP_HD void load_point_sample(const PairConst &pc, c
 
 // with_tail = false: the candidates (R, t, f0, f1) are returned WITHOUT the triangulation / depth-fit tail; the device
 // loop runs that tail in minimal_tail_kernel, one thread per candidate (mp_minimal.cu)
+// defer_pose (two focals, with_tail = false only): the candidate carries E in Model::R and no pose yet; the device loop
+// runs recoverPose -- 28 triangulations per candidate -- in recover_pose_warp_kernel, one warp per candidate
 template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 *M, const int *idx, unsigned mflags,
-                                             Model *out, bool with_tail = true) {
+                                             Model *out, bool with_tail = true, bool defer_pose = false) {
     constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
     double b0[NPT][3], b1[NPT][3], p0[NPT][2], p1[NPT][2], d0[NPT], d1[NPT];
     load_point_sample<KIND, NPT>(pc, M, idx, b0, b1, p0, p1, d0, d1);
@@ -249,7 +251,12 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
             for (int i = 0; i < 3; i++)
                 for (int j = 0; j < 3; j++) E[3 * i + j] = Fs[q][3 * i + j] * (i < 2 ? f1 : 1.0) * (j < 2 ? f0 : 1.0);
             Model m;
-            recover_pose<NPT>(E, p0, p1, 1e9, m.R, m.t); // un-calibrated points with K = I, as the reference does
+            if (defer_pose && !with_tail) {
+                for (int k = 0; k < 9; k++) m.R[k] = E[k];
+                m.t[0] = m.t[1] = m.t[2] = 0.0;
+            } else {
+                recover_pose<NPT>(E, p0, p1, 1e9, m.R, m.t); // un-calibrated points with K = I, as the reference does
+            }
             m.f0 = f0; m.f1 = f1;
             if (!with_tail) { m.scale = 1; m.o0 = 0; m.o1 = 0; out[n++] = m; continue; }
             if (depth_fit_tail<NPT>(pc, d0, d1, p0, p1, f0, f1, mflags, &m)) out[n++] = m;

@@ -298,37 +298,46 @@ MP_HD void bougnoux_focals(const double *F, double *f1sq, double *f2sq) {
 // cv::recoverPose(E, pts0, pts1, I, R, t, dist): candidates (R1,t),(R2,t),(R1,-t),(R2,-t);
 // every point is DLT-triangulated, a point counts when it lies in front of both cameras
 // and closer than dist; the first candidate with the largest count wins.
-template <int NP> MP_HD void recover_pose(const double *E, const double (*p0)[2], const double (*p1)[2], double dist,
-                                          double *R, double *t) {
-    double Ra[9], Rb[9], tt[3];
-    essential_factor(E, Ra, Rb, tt);
+// one (pose hypothesis c, point) test of recoverPose: c = 0..3 -> (Ra,t), (Rb,t), (Ra,-t), (Rb,-t)
+MP_HD bool recover_pose_point_ok(const double *Ra, const double *Rb, const double *tt, int c, const double *p0, const double *p1,
+                                 double dist) {
     const double P0[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
-    int best = -1, bestc = 0;
-    for (int c = 0; c < 4; c++) {
-        const double *Rc = (c & 1) ? Rb : Ra;
-        const double sg = c < 2 ? 1.0 : -1.0;
-        double P1[12];
-        for (int i = 0; i < 3; i++) {
-            for (int j = 0; j < 3; j++) P1[4 * i + j] = Rc[3 * i + j];
-            P1[4 * i + 3] = sg * tt[i];
-        }
-        int good = 0;
-        for (int i = 0; i < NP; i++) {
-            double Q[4];
-            triangulate_h(P0, P1, p0[i], p1[i], Q);
-            bool ok = Q[2] * Q[3] > 0;
-            const double X[3] = {Q[0] / Q[3], Q[1] / Q[3], Q[2] / Q[3]};
-            ok = ok && X[2] < dist;
-            const double z1 = P1[8] * X[0] + P1[9] * X[1] + P1[10] * X[2] + P1[11];
-            ok = ok && z1 > 0 && z1 < dist;
-            good += ok ? 1 : 0;
-        }
-        if (best < 0 || good > bestc) { best = c; bestc = good; }
+    const double *Rc = (c & 1) ? Rb : Ra;
+    const double sg = c < 2 ? 1.0 : -1.0;
+    double P1[12];
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) P1[4 * i + j] = Rc[3 * i + j];
+        P1[4 * i + 3] = sg * tt[i];
     }
+    double Q[4];
+    triangulate_h(P0, P1, p0, p1, Q);
+    bool ok = Q[2] * Q[3] > 0;
+    const double X[3] = {Q[0] / Q[3], Q[1] / Q[3], Q[2] / Q[3]};
+    ok = ok && X[2] < dist;
+    const double z1 = P1[8] * X[0] + P1[9] * X[1] + P1[10] * X[2] + P1[11];
+    ok = ok && z1 > 0 && z1 < dist;
+    return ok;
+}
+// the winner of the four counts: the first candidate with the largest count
+MP_HD void recover_pose_select(const double *Ra, const double *Rb, const double *tt, const int *good4, double *R, double *t) {
+    int best = -1, bestc = 0;
+    for (int c = 0; c < 4; c++)
+        if (best < 0 || good4[c] > bestc) { best = c; bestc = good4[c]; }
     const double *Rc = (best & 1) ? Rb : Ra;
     const double sg = best < 2 ? 1.0 : -1.0;
     for (int k = 0; k < 9; k++) R[k] = Rc[k];
     for (int k = 0; k < 3; k++) t[k] = sg * tt[k];
+}
+template <int NP> MP_HD void recover_pose(const double *E, const double (*p0)[2], const double (*p1)[2], double dist,
+                                          double *R, double *t) {
+    double Ra[9], Rb[9], tt[3];
+    essential_factor(E, Ra, Rb, tt);
+    int good[4];
+    for (int c = 0; c < 4; c++) {
+        good[c] = 0;
+        for (int i = 0; i < NP; i++) good[c] += recover_pose_point_ok(Ra, Rb, tt, c, p0[i], p1[i], dist) ? 1 : 0;
+    }
+    recover_pose_select(Ra, Rb, tt, good, R, t);
 }
 
 } // namespace mp
