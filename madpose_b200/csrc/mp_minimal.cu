@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
     const int p = first + item / LP_BMAX, b = item % LP_BMAX;
     PairWork &W = L.wk[p];
     const PairConst &pc = L.pc[p];
-    constexpr int MM = SOLVER == 0 ? kMaxModelsAffine[KIND] : kMaxModelsPoints[KIND];
+    constexpr int MM = SOLVER == 0 ? kMaxModelsAffine[KIND] : (KIND == TWO ? 8 : kMaxModelsPoints[KIND]); // TWO: + spare slots
     Model tmp[MM];
     const unsigned mflags = minimal_flags(prm.cfg, prm.opt);
     Model *out = L.models + ((size_t)p * LP_BMAX + b) * LP_MM;
@@ -203,6 +203,9 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
                                      : minimal_points<KIND>(pc, L.M + pc.off, W.idx[b], mflags, tmp, false, KIND == TWO);
         W.count[b] = c;
         for (int j = 0; j < c; j++) out[j] = tmp[j];
+        if (KIND == TWO)
+            for (int j = 0; j < c; j++)
+                for (int k = 0; k < 9; k++) out[j + 4].R[k] = tmp[j + 4].R[k]; // second rotation of E's factorisation
         if (c > 0) {
             const int base = atomicAdd(L.n_cand + grp, c);
             int *cl = L.cand + (size_t)first * LP_BMAX * LP_MM;
@@ -213,8 +216,8 @@ __global__ void __launch_bounds__(64, MP_MIN_CTAS) minimal_batch_kernel(LoopBuff
 
 // cv::recoverPose (...two_focal_estimator.cpp:143) for the candidates of the 7-point solver, ONE WARP per candidate:
 // lane = (pose hypothesis c, point i), 28 of 32 lanes triangulate one point each (one thread per sample walked the 84
-// triangulations of its <= 3 candidates in sequence: 32 % of the GPU time of configs[2]).  The candidate arrives with E in
-// Model::R (minimal_points, defer_pose); every lane factors E redundantly, the votes are one ballot.
+// triangulations of its <= 3 candidates in sequence: 32 % of the GPU time of configs[2]).  The candidate arrives with the
+// factors of E (minimal_points, defer_pose); the votes are one ballot.
 __global__ void __launch_bounds__(128) recover_pose_warp_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -227,9 +230,9 @@ __global__ void __launch_bounds__(128) recover_pose_warp_kernel(LoopBuffers L, c
         const PairConst &pc = L.pc[p];
         const PairWork &W = L.wk[p];
         Model *slot = L.models + ((size_t)p * LP_BMAX + b) * LP_MM + j;
-        double E[9], Ra[9], Rb[9], tt[3];
-        for (int k = 0; k < 9; k++) E[k] = slot->R[k];
-        essential_factor(E, Ra, Rb, tt);
+        double Ra[9], Rb[9], tt[3]; // the factors of E, left by minimal_batch_kernel<TWO, 1> (Rb in the spare slot j + 4)
+        for (int k = 0; k < 9; k++) { Ra[k] = slot->R[k]; Rb[k] = slot[4].R[k]; }
+        for (int k = 0; k < 3; k++) tt[k] = slot->t[k];
         bool ok = false;
         if (lane < 28) {
             const Match64 m = L.M[pc.off + W.idx[b][lane % 7]];
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(128) recover_pose_warp_kernel(LoopBuffers L, c
             ok = recover_pose_point_ok(Ra, Rb, tt, lane / 7, p0, p1, 1e9);
         }
         const unsigned votes = __ballot_sync(0xffffffffu, ok);
-        if (lane == 0) { // (every lane read E before the ballot)
+        if (lane == 0) { // (every lane read the factors before the ballot)
             int good[4];
             for (int c = 0; c < 4; c++) good[c] = __popc((votes >> (7 * c)) & 0x7fu);
             recover_pose_select(Ra, Rb, tt, good, slot->R, slot->t);

@@ -207,8 +207,9 @@ template <int KIND, int NPT> MP_HD void load_point_sample(const PairConst &pc, c
 
 // with_tail = false: the candidates (R, t, f0, f1) are returned WITHOUT the triangulation / depth-fit tail; the device
 // loop runs that tail in minimal_tail_kernel, one thread per candidate (mp_minimal.cu)
-// defer_pose (two focals, with_tail = false only): the candidate carries E in Model::R and no pose yet; the device loop
-// runs recoverPose -- 28 triangulations per candidate -- in recover_pose_warp_kernel, one warp per candidate
+// defer_pose (two focals, with_tail = false only): the candidate carries the factors of E (Ra in Model::R, t, and Rb in
+// out[n + 4].R: `out` must hold 8 models) and no pose yet; the device loop runs recoverPose -- 28 triangulations per
+// candidate -- in recover_pose_warp_kernel, one warp per candidate
 template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 *M, const int *idx, unsigned mflags,
                                              Model *out, bool with_tail = true, bool defer_pose = false) {
     constexpr int NPT = KIND == CALIB ? 5 : (KIND == SHARED ? 6 : 7);
@@ -251,9 +252,9 @@ template <int KIND> MP_HD int minimal_points(const PairConst &pc, const Match64 
             for (int i = 0; i < 3; i++)
                 for (int j = 0; j < 3; j++) E[3 * i + j] = Fs[q][3 * i + j] * (i < 2 ? f1 : 1.0) * (j < 2 ? f0 : 1.0);
             Model m;
-            if (defer_pose && !with_tail) {
-                for (int k = 0; k < 9; k++) m.R[k] = E[k];
-                m.t[0] = m.t[1] = m.t[2] = 0.0;
+            if (defer_pose && !with_tail) { // factors of E: Ra, t here, Rb in the spare slot n + 4 (the kind uses <= 4 slots)
+                Model &spare = out[n + 4];
+                essential_factor(E, m.R, spare.R, m.t);
             } else {
                 recover_pose<NPT>(E, p0, p1, 1e9, m.R, m.t); // un-calibrated points with K = I, as the reference does
             }
