@@ -319,7 +319,7 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaEventElapsedTime(&k, c->ev[1], c->ev[2]));
     MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));
     c->last_kernel_ms = k; c->last_total_ms = t; c->last_launches = launches;
-    if (trace) {
+    if (trace && c->phase_clk[8] != 0) { // sections of the LM driver: recorded by builds with -DMP_LM_PROF only
         const char *nm[8] = {"feed", "propose:setup", "cholesky", "forward", "backward", "model-change", "plus", "first"};
         for (int i = 0; i < 8; i++) fprintf(stderr, "[mp] LM driver %-14s %8.3f Gcycles\n", nm[i], c->phase_clk[8 + i] / 1e9);
     }

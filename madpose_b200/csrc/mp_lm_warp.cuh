@@ -78,8 +78,14 @@ __device__ __forceinline__ double warp_grad_max(const LmSetup &L, const double *
 }
 
 // LmDriver::first
+// cycles per driver section (printed under MP_TRACE=1): a build with -DMP_LM_PROF only, the reads cost ~2 % of the driver
+#ifdef MP_LM_PROF
 #define LMW_T0() long long lmw_t_ = clock64()
 #define LMW_T(slot_) do { if (lane == 0) { const long long n_ = clock64(); d.prof[slot_] += (unsigned long long)(n_ - lmw_t_); lmw_t_ = n_; } } while (0)
+#else
+#define LMW_T0() do { } while (0)
+#define LMW_T(slot_) do { } while (0)
+#endif
 static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
     const LmSetup &L = *d.L;
     LMW_T0();
@@ -175,6 +181,7 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
             if (lane == 0) d.wr[k] = rk;
 #pragma unroll
             for (int q = 0; q < 3; q++) {
+                if (q == 2 && nt < LM_NT) break; // entries 64, 65 belong to row 10: the two-focal kind only (uniform)
                 const int i = ei[q], j = ej[q];
                 if (i < nt && i > k && j >= k) {
                     const double lik = M[i * S + k] * rk; // a_ik = l_ik d_k
