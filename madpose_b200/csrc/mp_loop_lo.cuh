@@ -232,39 +232,42 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
         // step k and holds the value that sat at position j_k just before step k:
         //   a(i)   = value at position i just before step i = a(i') for the latest i' < i with j_i' == i, else v0[i]
         //   out[k] = a(k) if j_k == k, else a(q) for the latest q < k with j_q == j_k, else v0[j_k]
-        // "latest earlier swap with the same target" = the predecessor in the list of swaps sorted by
-        // (target, time): bitonic sort of the keys (j_i << 10 | i) in shared memory.
-        int P = 1;
-        while (P < head) P <<= 1;
-        unsigned *key = reinterpret_cast<unsigned *>(sh->sh_key);
-        int *ps = sh->sh_val, *pt = sh->sh_val + SH_MAXHEAD;
-        for (int k = threadIdx.x; k < P; k += blockDim.x)
-            key[k] = k < head ? ((unsigned)sh->sh_j[k] << 10) | (unsigned)k : 0xffffffffu;
+        // "latest earlier swap with the same target" = the largest time i < k with j_i == (j_k or k).  The swaps are
+        // grouped by target through 1024 hash buckets (count, scan, scatter: the order inside a bucket is arbitrary and
+        // does not matter, a bucket holds ~head / 1024 <= 1 swaps on average) and each query scans one bucket for the
+        // maximum -- 8 barriers instead of the 55 stages of a bitonic sort of the (target, time) keys.
+        constexpr int NB = 1024;
+        int *start = sh->sh_key, *ent = sh->sh_key + NB;           // bucket offsets (exclusive scan), swap times by bucket
+        int *ps = sh->sh_val, *pt = sh->sh_val + SH_MAXHEAD;       // pt doubles as the scatter cursors first
+        for (int b = threadIdx.x; b < NB; b += blockDim.x) start[b] = 0;
         __syncthreads();
-        for (int kk = 2; kk <= P; kk <<= 1)
-            for (int jj = kk >> 1; jj > 0; jj >>= 1) {
-                for (int t = threadIdx.x; t < P / 2; t += blockDim.x) {
-                    const int lo = ((t & ~(jj - 1)) << 1) | (t & (jj - 1)), hi = lo | jj;
-                    const unsigned x = key[lo], y = key[hi];
-                    const bool up = (lo & kk) == 0;
-                    if ((x > y) == up) { key[lo] = y; key[hi] = x; }
-                }
-                __syncthreads();
-            }
-        auto lower_bound = [&](unsigned want) { // first sorted position with key >= want
-            int lo = 0, hi = head;
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (key[mid] < want) lo = mid + 1; else hi = mid;
-            }
-            return lo;
-        };
-        for (int s2 = threadIdx.x; s2 < head; s2 += blockDim.x) {
-            const unsigned kq = key[s2];
-            ps[kq & 1023u] = (s2 > 0 && (key[s2 - 1] >> 10) == (kq >> 10)) ? (int)(key[s2 - 1] & 1023u) : -1;
-            const int u = lower_bound(((unsigned)s2 << 10) | (unsigned)s2) - 1; // here s2 plays the role of position i
-            pt[s2] = (u >= 0 && (key[u] >> 10) == (unsigned)s2) ? (int)(key[u] & 1023u) : -1;
+        for (int k = threadIdx.x; k < head; k += blockDim.x) atomicAdd(&start[sh->sh_j[k] & (NB - 1)], 1);
+        __syncthreads();
+        { // exclusive scan of the 1024 counts: a contiguous run per thread, warp scan, warp totals through sh->wcnt
+            const int per = NB / (int)blockDim.x, b0 = threadIdx.x * per; // blockDim is 32, 64 or 128
+            int run = 0;
+            for (int q = 0; q < per; q++) run += start[b0 + q];
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            int inc = run;
+            for (int dd = 1; dd < 32; dd <<= 1) { const int u = __shfl_up_sync(0xffffffffu, inc, dd); if (lane >= dd) inc += u; }
+            if (lane == 31) sh->wcnt[0][warp] = inc;
+            __syncthreads();
+            int base = inc - run;
+            for (int w = 0; w < warp; w++) base += sh->wcnt[0][w];
+            for (int q = 0; q < per; q++) { const int c = start[b0 + q]; start[b0 + q] = base; pt[b0 + q] = base; base += c; }
         }
+        __syncthreads();
+        for (int k = threadIdx.x; k < head; k += blockDim.x) ent[atomicAdd(&pt[sh->sh_j[k] & (NB - 1)], 1)] = k;
+        __syncthreads();
+        auto latest_before = [&](int target, int before) { // max i < before with j_i == target, or -1
+            const int b = target & (NB - 1), e1 = b + 1 < NB ? start[b + 1] : head;
+            int best = -1;
+            for (int e = start[b]; e < e1; e++) { const int i = ent[e]; if (i < before && i > best && sh->sh_j[i] == target) best = i; }
+            return best;
+        };
+        // (the cursors in pt are dead after the barrier above; the queries read start / ent / sh_j only)
+        for (int k = threadIdx.x; k < head; k += blockDim.x) { ps[k] = latest_before(sh->sh_j[k], k); pt[k] = latest_before(k, k); }
+        const int last_hit = (head == n - 1 && n - 1 < target) ? latest_before(n - 1, head) : -1; // (every swap time is < head)
         __syncthreads();
         auto a_of = [&](int c) {
             while (pt[c] >= 0) c = pt[c];
@@ -277,10 +280,7 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
             else { const int q = ps[k]; out = q >= 0 ? a_of(q) : sh->sh_vj[k]; }
             v[k] = out;
         }
-        if (threadIdx.x == 0 && head == n - 1 && n - 1 < target) { // the list grows: its last element is kept too
-            const int u = lower_bound((unsigned)n << 10) - 1;
-            if (u >= 0 && (key[u] >> 10) == (unsigned)(n - 1)) v[n - 1] = a_of((int)(key[u] & 1023u));
-        }
+        if (threadIdx.x == 0 && last_hit >= 0) v[n - 1] = a_of(last_hit); // the list grows: its last element is kept too
     }
     __syncthreads();
     // resize: shrink, or grow with zeros (quirk Q3)
