@@ -213,6 +213,9 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     if (!serial)
         for (int k = 0; k < NSIDE; k++) MP_CUDA(cudaStreamWaitEvent(c->sstream[k], c->ev_init, 0));
     int side_rr = 0;
+    // CTA widths of the local optimisation each group needs (bit 0: pairs below LP_WIDE_N matches, bit 1: the others)
+    std::vector<int> lo_widths(G, 0);
+    for (int p = 0; p < n_pairs; p++) lo_widths[p / gsz] |= (c->off[p + 1] - c->off[p]) >= LP_WIDE_N ? 2 : 1;
     const long long *d_off3 = A.off3.as<long long>();
     const int *d_caps = A.caps.as<int>();
     auto enqueue_round = [&](int g, int slot) -> int {
@@ -242,9 +245,9 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
             ss = c->sstream[side_rr++ % NSIDE];
             MP_CUDA(cudaStreamWaitEvent(ss, c->gev[g], 0));
         }
-        if (kind == CALIB) MP_CUDA(launch_lo_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, ss));
-        else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, ss));
-        else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, ss));
+        if (kind == CALIB) MP_CUDA(launch_lo_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
+        else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
+        else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
         if (serial) MP_CUDA(tick(-1));
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot), L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot) + 1, L.n_ret + g, sizeof(int), cudaMemcpyDeviceToHost, ss));

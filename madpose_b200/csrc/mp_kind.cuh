@@ -193,7 +193,10 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
 }
 
 // lo_kernel: local optimisations and the final stage of the pairs holding a ticket of a round <= `round`.
-template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM) lo_kernel(LoopBuffers L, const LoopParams *prmp,
+// THREADS: LP_THREADS (pairs below LP_WIDE_N matches, two CTAs per SM) or LP_WIDE_THREADS (the others, one per SM); a CTA
+// of the wrong width for its pair leaves at once (the host launches a width only when the group holds such pairs).
+template <int KIND, int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == LP_THREADS ? LP_CTAS_PER_SM : 1) lo_kernel(LoopBuffers L, const LoopParams *prmp,
                                                                               const long long *off3, const int *caps, int first, int round) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
@@ -201,6 +204,7 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
     __shared__ int claimed;
     const LoopParams &prm = *prmp;
     const int p = first + blockIdx.x;
+    if ((L.pc[p].n >= LP_WIDE_N) != (THREADS == LP_WIDE_THREADS)) return;
     if (threadIdx.x == 0) {
         const int t = *reinterpret_cast<volatile int *>(L.lo_req + p);
         claimed = (t > 0 && t <= round && atomicCAS(L.lo_req + p, t, -t) == t) ? 1 : 0;
@@ -319,11 +323,13 @@ cudaError_t launch_scan_kind(LoopBuffers L, const LoopParams *dprm, int first, i
 }
 template <int KIND>
 cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
-                           const int *caps, int round, cudaStream_t s) {
+                           const int *caps, int round, int widths, cudaStream_t s) {
     // CTA size of the local optimisation: 128 measured best on configs[1] (64: 4 CTAs per SM but 12 % slower per step,
-    // 32: worse); MP_LO_THREADS overrides it for experiments
+    // 32: worse); MP_LO_THREADS overrides it for experiments.  widths: bit 0 = the group holds pairs below LP_WIDE_N
+    // matches, bit 1 = pairs from LP_WIDE_N on (LP_WIDE_THREADS threads, mp_loop.cuh)
     static const int lo_threads = [] { const char *e = getenv("MP_LO_THREADS"); const int v = e ? atoi(e) : LP_THREADS; return (v == 32 || v == 64 || v == 128) ? v : LP_THREADS; }();
-    lo_kernel<KIND><<<count, lo_threads, 0, s>>>(L, dprm, off3, caps, first, round);
+    if (widths & 1) lo_kernel<KIND, LP_THREADS><<<count, lo_threads, 0, s>>>(L, dprm, off3, caps, first, round);
+    if (widths & 2) lo_kernel<KIND, LP_WIDE_THREADS><<<count, LP_WIDE_THREADS, 0, s>>>(L, dprm, off3, caps, first, round);
     return cudaGetLastError();
 }
 

@@ -25,8 +25,20 @@ constexpr int LP_BMAX = 256;           // iterations per pair per round (upper b
                                        // its batch after every round without a new best model)
 constexpr int LP_B0 = 64, LP_BDEF = 128; // measured on configs[1]: cap 64 -> 179-185 ms, 128 -> 178-181, 256 -> 183-187
 constexpr int LP_MM = kMaxModelsAny;   // model slots per iteration
-constexpr int LP_THREADS = 128;        // decide_kernel CTA
-constexpr int LP_CTAS_PER_SM = 2;
+#ifndef MP_LP_THREADS
+#define MP_LP_THREADS 128
+#endif
+constexpr int LP_THREADS = MP_LP_THREADS; // CTA of the scan / local-optimisation kernels
+#ifndef MP_LO_CTAS
+#define MP_LO_CTAS 2
+#endif
+constexpr int LP_CTAS_PER_SM = MP_LO_CTAS;
+// Local optimisation of a pair with >= LP_WIDE_N matches runs on a CTA of LP_WIDE_THREADS threads (one per SM): the passes
+// over the matches take half the time, the LM driver does not care.  The width is a function of the PAIR alone (never of
+// the batch or the schedule), so a pair's result does not depend on what it is batched with.  Measured (ms / step, all
+// pairs at 128 | all at 256 threads): configs[1] (2k matches) 124.9 | 133.5, configs[2] (5k) 266.7 | 255.3, configs[3]
+// (10k) 154.0 | 125.3.
+constexpr int LP_WIDE_N = 4096, LP_WIDE_THREADS = 256;
 enum { PH_ITER = 0, PH_LO_PRE = 1, PH_LO_MAIN = 2, PH_FINISH = 3, PH_DONE = 4, PH_BUSY = 5 };
 
 struct LoopParams {

@@ -13,7 +13,7 @@ constexpr int SH_MAXHEAD = 1024, SH_TAB = 2048;
 
 struct BlockScratch { // shared memory of the decide kernel
     double red[32];
-    double part[LP_THREADS / 32][LM_ACC_DOUBLES];
+    double part[LP_WIDE_THREADS / 32][LM_ACC_DOUBLES];
     double total[LM_ACC_DOUBLES];
     int cnt[3], wcnt[3][16];
     int flag[4], base_len, fit_len, fit_cnt[3];

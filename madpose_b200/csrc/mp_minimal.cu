@@ -141,7 +141,10 @@ __global__ void __launch_bounds__(W6_WARPS * 32) minimal6_warp_kernel(const Pair
 #ifndef W6B_WARPS
 #define W6B_WARPS 12   // warps per CTA of the loop's kernel: one CTA per SM, stages in lockstep
 #endif
-__global__ void __launch_bounds__(W6B_WARPS * 32, 1) minimal6_warp_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
+#ifndef W6B_CTAS
+#define W6B_CTAS 1      // resident CTAs per SM the kernel is compiled for
+#endif
+__global__ void __launch_bounds__(W6B_WARPS * 32, W6B_CTAS) minimal6_warp_batch_kernel(LoopBuffers L, const LoopParams *prmp, int first, int count) {
     extern __shared__ __align__(16) unsigned char w6_smem[];
     Warp6Work *work = reinterpret_cast<Warp6Work *>(w6_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -312,7 +315,7 @@ cudaError_t launch_minimal_batch(LoopBuffers L, const LoopParams *dprm, int firs
     }
     if (warp6) { // grid-stride over the list: enough CTAs to fill the machine, no more than the list can use
         const long long want = (ib + W6B_WARPS - 1) / W6B_WARPS;
-        const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count));
+        const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sm_count * W6B_CTAS));
         // (function attributes are per device: set on every launch, the call is cheap)
         const cudaError_t attr = cudaFuncSetAttribute(minimal6_warp_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                       (int)(W6B_WARPS * sizeof(Warp6Work)));
