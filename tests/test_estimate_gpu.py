@@ -352,3 +352,26 @@ def test_schedule_invariance(ctx):
                     np.testing.assert_array_equal(x, y)
     finally:
         ctx.set_batch(0); ctx.set_groups(0)
+
+
+def test_mixed_width_batch_is_batch_invariant(ctx):
+    """Local optimisation runs on 256-thread CTAs for pairs with >= 4096 matches and on 128-thread CTAs for the others
+    (LP_WIDE_N, mp_loop.cuh); the width depends on the pair alone.  A batch mixing both classes must give every pair the
+    bits it gets when estimated alone or with pairs of its own class only."""
+    sizes = [900, 4096, 1500, 6000, 4095, 5200, 300, 4500]
+    ps = [problem(0, p=i, n=n) for i, n in enumerate(sizes)]
+    kind, opt, cfg = ps[0][0]["kind"], ps[0][2], ps[0][3]
+    pairs = [q[1] for q in ps]
+
+    def sig(m, s, inl):
+        return [(tuple(m[i]), s[i].num_iterations_total, s[i].number_lo_iterations, s[i].best_model_score,
+                 tuple(int(x) for x in s[i].num_inliers), tuple(a.tobytes() for a in inl[i])) for i in range(len(s))]
+
+    mixed = sig(*ctx.estimate_batch(kind, pairs, opt, cfg))
+    assert any(s_[2] > 0 for s_ in mixed)  # local optimisations did run
+    for i, p in enumerate(pairs):  # alone
+        assert sig(*ctx.estimate_batch(kind, [p], opt, cfg))[0] == mixed[i], f"pair {i} (n = {sizes[i]}) differs when estimated alone"
+    for cls in (False, True):  # with its own width class only
+        idx = [i for i, n in enumerate(sizes) if (n >= 4096) == cls]
+        got = sig(*ctx.estimate_batch(kind, [pairs[i] for i in idx], opt, cfg))
+        assert got == [mixed[i] for i in idx]
