@@ -174,6 +174,8 @@ void mp_destroy(mp_ctx *c) {
     for (auto &e : c->sev) cudaEventDestroy(e);
     for (auto &g : c->gstream) cudaStreamDestroy(g);
     for (auto &g : c->sstream) cudaStreamDestroy(g);
+    for (auto &g : c->hstream) cudaStreamDestroy(g);
+    for (auto &e : c->hev) cudaEventDestroy(e);
     if (c->ev_init) cudaEventDestroy(c->ev_init);
     if (c->loop_alloc) delete static_cast<mp::LoopAlloc *>(c->loop_alloc);
     if (c->stream) cudaStreamDestroy(c->stream);

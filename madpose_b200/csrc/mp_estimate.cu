@@ -138,6 +138,18 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         MP_CUDA(cudaStreamCreateWithPriority(&gs, cudaStreamNonBlocking, prio_mode == 2 ? prio_hi : prio_lo));
         c->sstream.push_back(gs);
     }
+    // Local optimisations of pairs that already have 2 or more behind them are launched on high-priority streams: the
+    // step ends with the pairs that need 8-11 of them (2.8 on average), each a ~5 ms chain, and their CTAs should not
+    // queue behind the others'.  Scheduling only -- a pair's result does not depend on it.  Measured on three 1500-pair
+    // ranges of configs[1]: 124.6 / 134.4 / 133.1 -> 125.0 / 132.0 / 131.2 ms per step.  MP_LO_HEAVY = k overrides the
+    // threshold (0 = off).
+    static const int heavy_from = [] { const char *e = getenv("MP_LO_HEAVY"); return e ? atoi(e) : 2; }();
+    while (heavy_from > 0 && (int)c->hstream.size() < NSIDE) {
+        cudaStream_t hs; cudaEvent_t he;
+        MP_CUDA(cudaStreamCreateWithPriority(&hs, cudaStreamNonBlocking, prio_hi));
+        MP_CUDA(cudaEventCreateWithFlags(&he, cudaEventDisableTiming));
+        c->hstream.push_back(hs); c->hev.push_back(he);
+    }
     while ((int)c->sev.size() < G * SLOTS) {
         cudaEvent_t ge;
         MP_CUDA(cudaEventCreateWithFlags(&ge, cudaEventDisableTiming));
@@ -240,15 +252,19 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         else MP_CUDA(launch_scan_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, gs));
         MP_CUDA(cudaMemcpyAsync(h_iter + g, L.n_iter + g, sizeof(int), cudaMemcpyDeviceToHost, gs));
         MP_CUDA(cudaEventRecord(c->gev[g], gs));
-        cudaStream_t ss = gs;
+        cudaStream_t ss = gs, hs = nullptr;
+        int hk = -1;
         if (!serial) {
-            ss = c->sstream[side_rr++ % NSIDE];
+            const int k = side_rr++ % NSIDE;
+            ss = c->sstream[k];
             MP_CUDA(cudaStreamWaitEvent(ss, c->gev[g], 0));
+            if (heavy_from > 0) { hk = k; hs = c->hstream[k]; MP_CUDA(cudaStreamWaitEvent(hs, c->gev[g], 0)); }
         }
-        if (kind == CALIB) MP_CUDA(launch_lo_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
-        else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
-        else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss));
+        if (kind == CALIB) MP_CUDA(launch_lo_kind<CALIB>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss, hs, heavy_from));
+        else if (kind == SHARED) MP_CUDA(launch_lo_kind<SHARED>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss, hs, heavy_from));
+        else MP_CUDA(launch_lo_kind<TWO>(L, dprm, first, count, d_off3, d_caps, round, lo_widths[g], ss, hs, heavy_from));
         if (serial) MP_CUDA(tick(-1));
+        if (hs) { MP_CUDA(cudaEventRecord(c->hev[hk], hs)); MP_CUDA(cudaStreamWaitEvent(ss, c->hev[hk], 0)); } // the slot is done when both are
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot), L.n_active + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaMemcpyAsync(h_side + 2 * (g * SLOTS + slot) + 1, L.n_ret + g, sizeof(int), cudaMemcpyDeviceToHost, ss));
         MP_CUDA(cudaEventRecord(c->sev[g * SLOTS + slot], ss));

@@ -24,7 +24,7 @@ cudaError_t launch_scan_kind(LoopBuffers L, const LoopParams *dprm, int first, i
                              const int *caps, int round, cudaStream_t s);
 template <int KIND>
 cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
-                           const int *caps, int round, int widths, cudaStream_t s);
+                           const int *caps, int round, int widths, cudaStream_t s, cudaStream_t s_heavy, int heavy_from);
 template <int KIND>
 cudaError_t launch_lm_kind(const PairConst *pc, const Match64 *M, const LoopParams *dprm, int n_problems, const Model *start,
                            const int *idx, const int *off, Model *out, double *info, bool nonminimal, cudaStream_t s);

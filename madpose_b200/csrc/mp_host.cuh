@@ -82,7 +82,8 @@ struct mp_ctx {
     int trace_cap = 0;                        // mp_set_trace: events kept per pair (0 = tracing off)
     int batch_override = 0;                   // speculated iterations per pair per round, 0 = LP_BMAX
     std::vector<cudaStream_t> gstream, sstream; // per-group round pipelines; side streams of the lo_kernel launches
-    std::vector<cudaEvent_t> gev, sev;
+    std::vector<cudaEvent_t> gev, sev, hev;
+    std::vector<cudaStream_t> hstream; // high-priority twins of the side streams (heavy pairs' local optimisations)
     cudaEvent_t ev_init = nullptr;
     void *loop_alloc = nullptr; // mp::LoopAlloc, created on first mp_estimate_batch
     uint32_t tape_seed = 0;

@@ -197,7 +197,8 @@ template <int KIND> __global__ void __launch_bounds__(LP_THREADS, LP_CTAS_PER_SM
 // of the wrong width for its pair leaves at once (the host launches a width only when the group holds such pairs).
 template <int KIND, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == LP_THREADS ? LP_CTAS_PER_SM : 1) lo_kernel(LoopBuffers L, const LoopParams *prmp,
-                                                                              const long long *off3, const int *caps, int first, int round) {
+                                                                              const long long *off3, const int *caps, int first, int round,
+                                                                              int heavy_cls, int heavy_from) {
     __shared__ PairState S;
     __shared__ BlockScratch sh;
     __shared__ double lo_score;
@@ -205,6 +206,9 @@ __global__ void __launch_bounds__(THREADS, THREADS == LP_THREADS ? LP_CTAS_PER_S
     const LoopParams &prm = *prmp;
     const int p = first + blockIdx.x;
     if ((L.pc[p].n >= LP_WIDE_N) != (THREADS == LP_WIDE_THREADS)) return;
+    // heavy_cls: 0 = every pair; 1 / 2 = only the pairs that have run fewer than / at least heavy_from local optimisations
+    // so far (the launch on the high-priority stream takes the pairs with the long chains first: scheduling only)
+    if (heavy_cls != 0 && ((*reinterpret_cast<volatile int *>(&L.st[p].number_lo) >= heavy_from) != (heavy_cls == 2))) return;
     if (threadIdx.x == 0) {
         const int t = *reinterpret_cast<volatile int *>(L.lo_req + p);
         claimed = (t > 0 && t <= round && atomicCAS(L.lo_req + p, t, -t) == t) ? 1 : 0;
@@ -323,13 +327,19 @@ cudaError_t launch_scan_kind(LoopBuffers L, const LoopParams *dprm, int first, i
 }
 template <int KIND>
 cudaError_t launch_lo_kind(LoopBuffers L, const LoopParams *dprm, int first, int count, const long long *off3,
-                           const int *caps, int round, int widths, cudaStream_t s) {
+                           const int *caps, int round, int widths, cudaStream_t s, cudaStream_t s_heavy, int heavy_from) {
     // CTA size of the local optimisation: 128 measured best on configs[1] (64: 4 CTAs per SM but 12 % slower per step,
     // 32: worse); MP_LO_THREADS overrides it for experiments.  widths: bit 0 = the group holds pairs below LP_WIDE_N
-    // matches, bit 1 = pairs from LP_WIDE_N on (LP_WIDE_THREADS threads, mp_loop.cuh)
+    // matches, bit 1 = pairs from LP_WIDE_N on (LP_WIDE_THREADS threads, mp_loop.cuh).
+    // s_heavy != nullptr: the pairs with >= heavy_from local optimisations behind them go to that (high-priority) stream
     static const int lo_threads = [] { const char *e = getenv("MP_LO_THREADS"); const int v = e ? atoi(e) : LP_THREADS; return (v == 32 || v == 64 || v == 128) ? v : LP_THREADS; }();
-    if (widths & 1) lo_kernel<KIND, LP_THREADS><<<count, lo_threads, 0, s>>>(L, dprm, off3, caps, first, round);
-    if (widths & 2) lo_kernel<KIND, LP_WIDE_THREADS><<<count, LP_WIDE_THREADS, 0, s>>>(L, dprm, off3, caps, first, round);
+    const int ncls = s_heavy ? 2 : 1;
+    for (int k = 0; k < ncls; k++) {
+        const int cls = s_heavy ? (k == 0 ? 2 : 1) : 0; // the heavy class is enqueued first
+        cudaStream_t st = (cls == 2) ? s_heavy : s;
+        if (widths & 1) lo_kernel<KIND, LP_THREADS><<<count, lo_threads, 0, st>>>(L, dprm, off3, caps, first, round, cls, heavy_from);
+        if (widths & 2) lo_kernel<KIND, LP_WIDE_THREADS><<<count, LP_WIDE_THREADS, 0, st>>>(L, dprm, off3, caps, first, round, cls, heavy_from);
+    }
     return cudaGetLastError();
 }
 

@@ -3,6 +3,6 @@
 namespace mp {
 template cudaError_t launch_score_kind<0>(LoopBuffers, const LoopParams *, int, int, int, size_t, cudaStream_t);
 template cudaError_t launch_scan_kind<0>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, int, cudaStream_t);
-template cudaError_t launch_lo_kind<0>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, int, int, cudaStream_t);
+template cudaError_t launch_lo_kind<0>(LoopBuffers, const LoopParams *, int, int, const long long *, const int *, int, int, cudaStream_t, cudaStream_t, int);
 template cudaError_t launch_lm_kind<0>(const PairConst *, const Match64 *, const LoopParams *, int, const Model *, const int *, const int *, Model *, double *, bool, cudaStream_t);
 }
