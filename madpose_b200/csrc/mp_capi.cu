@@ -1,6 +1,7 @@
 // C ABI of madpose_b200 (include/madpose_b200.h).  Every entry point runs CUDA
 // kernels on the context's device; there is no CPU fallback.
 #include <cstdlib>
+#include <atomic>
 #include <thread>
 #include <vector>
 #include <algorithm>
@@ -61,10 +62,35 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
             }
         }
     };
-    { // the caller's arrays are pageable and scattered: pack them into the pinned staging buffers on several threads
+    // The caller's arrays are pageable and scattered: several threads pack them into the pinned staging buffers, and every
+    // thread sends a slice to the device as soon as it is packed (~64 k matches = 3 MB at a time), so the copies over the
+    // link run while the rest is still being packed.
+    cudaStream_t s = c->stream;
+    std::atomic<int> cuda_err{(int)cudaSuccess};
+    auto send_range = [&](int pa, int pb) {
+        const long long o = c->off[pa], m = c->off[pb] - o;
+        if (m <= 0) return;
+        cudaError_t e = cudaMemcpyAsync(c->d_x0.as<double>() + 2 * o, c->h_x0.as<double>() + 2 * o, 2 * m * sizeof(double), cudaMemcpyHostToDevice, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_x1.as<double>() + 2 * o, c->h_x1.as<double>() + 2 * o, 2 * m * sizeof(double), cudaMemcpyHostToDevice, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_d0.as<double>() + o, c->h_d0.as<double>() + o, m * sizeof(double), cudaMemcpyHostToDevice, s);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_d1.as<double>() + o, c->h_d1.as<double>() + o, m * sizeof(double), cudaMemcpyHostToDevice, s);
+        if (e != cudaSuccess) cuda_err.store((int)e);
+    };
+    auto pack_and_send = [&](int p0, int p1, bool set_device) {
+        if (set_device && cudaSetDevice(c->device) != cudaSuccess) { cuda_err.store((int)cudaErrorInvalidDevice); return; }
+        int pa = p0;
+        while (pa < p1) {
+            int pb = pa;
+            while (pb < p1 && c->off[pb] - c->off[pa] < 65536) pb++;
+            pack_range(pa, pb);
+            send_range(pa, pb);
+            pa = pb;
+        }
+    };
+    {
         int nt = (int)std::min<long long>(8, std::max<long long>(1, N / 200000));
         nt = std::min<int>(nt, std::max(1u, std::thread::hardware_concurrency()));
-        if (nt <= 1) pack_range(0, n_pairs);
+        if (nt <= 1) pack_and_send(0, n_pairs, false);
         else {
             std::vector<std::thread> th;
             int p0 = 0;
@@ -73,17 +99,14 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
                 const long long want = N * (t + 1) / nt;
                 while (p1 < n_pairs && c->off[p1 + 1] <= want) p1++;
                 if (t == nt - 1) p1 = n_pairs;
-                th.emplace_back(pack_range, p0, p1);
+                th.emplace_back(pack_and_send, p0, p1, true);
                 p0 = p1;
             }
             for (auto &x : th) x.join();
         }
     }
-    cudaStream_t s = c->stream;
-    MP_CUDA(cudaMemcpyAsync(c->d_x0.p, c->h_x0.p, 2 * N * sizeof(double), cudaMemcpyHostToDevice, s));
-    MP_CUDA(cudaMemcpyAsync(c->d_x1.p, c->h_x1.p, 2 * N * sizeof(double), cudaMemcpyHostToDevice, s));
-    MP_CUDA(cudaMemcpyAsync(c->d_d0.p, c->h_d0.p, N * sizeof(double), cudaMemcpyHostToDevice, s));
-    MP_CUDA(cudaMemcpyAsync(c->d_d1.p, c->h_d1.p, N * sizeof(double), cudaMemcpyHostToDevice, s));
+    if (cuda_err.load() != (int)cudaSuccess)
+        return fail(MP_ERR_CUDA, std::string("upload_pairs: host-to-device copy: ") + cudaGetErrorString((cudaError_t)cuda_err.load()));
     MP_CUDA(cudaMemcpyAsync(c->d_raw.p, c->h_raw.p, n_pairs * sizeof(PairRaw), cudaMemcpyHostToDevice, s));
     prep_pairs_kernel<<<n_pairs, 256, 0, s>>>(c->d_raw.as<PairRaw>(), c->d_x0.as<double>(), c->d_x1.as<double>(),
                                               c->d_d0.as<double>(), c->d_d1.as<double>(), c->d_pc.as<PairConst>(),

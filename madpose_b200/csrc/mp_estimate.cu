@@ -330,10 +330,29 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
     MP_CUDA(cudaMemcpyAsync(out_stats, A.out_stats.p, n_pairs * sizeof(mp_stats), cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaMemcpyAsync(c->phase_clk, L.clk, 128, cudaMemcpyDeviceToHost, s));
     c->last_groups = G;
-    if (out_inliers && N > 0)
-        MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, 3 * (size_t)N * sizeof(int), cudaMemcpyDeviceToHost, s));
+    // The caller's inlier buffer is pageable (and, when freshly allocated, not yet backed by pages): a direct copy goes
+    // through the driver's bounce buffers on one host thread.  Large lists land in a pinned buffer at link speed and are
+    // moved -- and the pages touched -- by several host threads.
+    const size_t inl_bytes = (out_inliers && N > 0) ? 3 * (size_t)N * sizeof(int) : 0;
+    const bool staged = inl_bytes >= (size_t)(4u << 20);
+    if (staged) {
+        MP_CUDA(c->h_inl.reserve(inl_bytes));
+        MP_CUDA(cudaMemcpyAsync(c->h_inl.p, A.inl_best.p, inl_bytes, cudaMemcpyDeviceToHost, s));
+    } else if (inl_bytes)
+        MP_CUDA(cudaMemcpyAsync(out_inliers, A.inl_best.p, inl_bytes, cudaMemcpyDeviceToHost, s));
     MP_CUDA(cudaEventRecord(c->ev[3], s));
     MP_CUDA(cudaStreamSynchronize(s));
+    if (staged) {
+        const int nt = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())), inl_bytes >> 22));
+        const size_t per = ((inl_bytes + nt - 1) / nt + 4095) & ~(size_t)4095;
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; t++) {
+            const size_t o = (size_t)t * per;
+            if (o >= inl_bytes) break;
+            th.emplace_back([=] { std::memcpy(reinterpret_cast<char *>(out_inliers) + o, c->h_inl.as<char>() + o, std::min(per, inl_bytes - o)); });
+        }
+        for (auto &x : th) x.join();
+    }
     float k = 0, t = 0;
     MP_CUDA(cudaEventElapsedTime(&k, c->ev[1], c->ev[2]));
     MP_CUDA(cudaEventElapsedTime(&t, c->ev[0], c->ev[3]));

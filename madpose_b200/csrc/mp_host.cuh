@@ -82,6 +82,7 @@ struct mp_ctx {
     int trace_cap = 0;                        // mp_set_trace: events kept per pair (0 = tracing off)
     int batch_override = 0;                   // speculated iterations per pair per round, 0 = LP_BMAX
     std::vector<cudaStream_t> gstream, sstream; // per-group round pipelines; side streams of the lo_kernel launches
+    mp::PinBuf h_inl;      // pinned landing buffer of the inlier lists (copied to the caller's pageable buffer by host threads)
     std::vector<cudaEvent_t> gev, sev, hev;
     std::vector<cudaStream_t> hstream; // high-priority twins of the side streams (heavy pairs' local optimisations)
     cudaEvent_t ev_init = nullptr;

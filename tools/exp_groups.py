@@ -9,7 +9,7 @@ config = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 kind, pairs, opt, cfg, keep = workload.make_batch(config, workload.CONFIG_INFO[config]["pairs"])
 ctx = capi.Context(0)
 ctx.upload_batch(kind, pairs, opt)
-for g, b in [(0, 0), (1, 0), (2, 0), (3, 0), (4, 0), (6, 0), (1, 256), (2, 256), (2, 64), (3, 64)]:
+for g, b in [(0, 0), (2, 0), (3, 0), (4, 0), (6, 0), (8, 0), (12, 0), (4, 32), (4, 64), (8, 32), (2, 32)]:
     ctx.set_groups(g); ctx.set_batch(b)
     ms = []
     for _ in range(4):
