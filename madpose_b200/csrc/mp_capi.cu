@@ -88,7 +88,8 @@ int upload_pairs(mp_ctx *c, int kind, int n_pairs, const mp_pair *pairs, const m
         }
     };
     {
-        int nt = (int)std::min<long long>(8, std::max<long long>(1, N / 200000));
+        static const int nt_cap = [] { const char *e = getenv("MP_PACK_THREADS"); const int v = e ? atoi(e) : 8; return v >= 1 && v <= 64 ? v : 8; }();
+        int nt = (int)std::min<long long>(nt_cap, std::max<long long>(1, N / 200000));
         nt = std::min<int>(nt, std::max(1u, std::thread::hardware_concurrency()));
         if (nt <= 1) pack_and_send(0, n_pairs, false);
         else {

@@ -34,8 +34,8 @@ __global__ void finalize_kernel(LoopBuffers L, int n_pairs, mp_model *models, mp
     stats[p] = o;
 }
 
-static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
-                        mp_stats *out_stats, int32_t *out_inliers, bool record_start) {
+static int run_estimate_impl(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
+                             mp_stats *out_stats, int32_t *out_inliers, bool record_start) {
     if (opt->num_lsq_iterations < 0 || opt->num_lo_steps < 0 || opt->min_sample_multiplicator < 0)
         return fail(MP_ERR_ARG, "negative LO option");
     if (c->resident_pairs <= 0) return fail(MP_ERR_ARG, "no resident batch: call mp_upload_batch first");
@@ -371,6 +371,20 @@ static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp
         c->class_ms[cls] += ms; c->class_launches[cls] += 1;
     }
     return MP_OK;
+}
+
+// An error inside the round loop returns with kernels and copies still in flight on the group and side streams, and the
+// next call would reuse their buffers: drain the device before handing the error to the caller.
+static int run_estimate(mp_ctx *c, LoopAlloc &A, const mp_options *opt, const mp_config *cfg, mp_model *out_models,
+                        mp_stats *out_stats, int32_t *out_inliers, bool record_start) {
+    const int rc = run_estimate_impl(c, A, opt, cfg, out_models, out_stats, out_inliers, record_start);
+    if (rc != MP_OK) {
+        const std::string msg = g_err; // (keep the first error's text)
+        cudaDeviceSynchronize();
+        cudaGetLastError();
+        g_err = msg;
+    }
+    return rc;
 }
 
 } // namespace mp
