@@ -90,12 +90,16 @@ static int run_estimate_impl(mp_ctx *c, LoopAlloc &A, const mp_options *opt, con
     LoopParams *prm = A.h_prm.as<LoopParams>();
     prm->opt = *opt; prm->cfg = *cfg; prm->n_pairs = n_pairs; // speculated iterations per pair per round: 128, or 256 for long loops (an iteration budget of thousands: every round
     // costs a fixed launch + solve latency; measured on configs[3], 64 pairs x ~7600 iterations: 176 -> 164 ms/step)
+    // Small calls (<= 256 pairs) are bound by the number of rounds, not by solver throughput: they speculate 256 iterations
+    // per round and restart at 128 after a local optimisation (measured, ms per call of 1 / 4 / 16 / 64 configs[1] pairs:
+    // 4.1 / 12.8 / 20.4 / 26.1 -> 3.8 / 11.9 / 18.9 / 24.7).  Scheduling only: results do not depend on it.
+    const bool small_call = n_pairs <= 256;
     prm->bmax = c->batch_override > 0 ? c->batch_override
-                                      : (std::max(opt->max_num_iterations, opt->min_num_iterations) >= 4096 ? LP_BMAX : LP_BDEF);
+                                      : ((small_call || std::max(opt->max_num_iterations, opt->min_num_iterations) >= 4096) ? LP_BMAX : LP_BDEF);
     {
         const char *e = getenv("MP_B_AFTER_LO"); // experiments
         const int v = e ? atoi(e) : 0;
-        prm->b_after_lo = std::min(v > 0 ? v : LP_B0, prm->bmax); // measured on configs[1] (bmax 64): 16 -> 245 ms, 32 -> 235, 64 -> 232
+        prm->b_after_lo = std::min(v > 0 ? v : (small_call ? 2 * LP_B0 : LP_B0), prm->bmax); // measured on configs[1] (bmax 64): 16 -> 245 ms, 32 -> 235, 64 -> 232
     } prm->guard = 1e-3;
     // Groups of consecutive pairs, each with its own round pipeline (sample -> minimal -> score -> scan) on its own
     // stream.  Local optimisations and the final stage run in lo_kernel launches on side streams, so a round never

@@ -9,6 +9,7 @@ from madpose_b200 import capi, workload
 config = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 sizes = [int(v) for v in sys.argv[2:]] or [workload.CONFIG_INFO[config]["pairs"]]
 ctx = capi.Context(0)
+if os.environ.get("MP_SET_BATCH"): ctx.set_batch(int(os.environ["MP_SET_BATCH"]))
 for n in sizes:
     kind, pairs, opt, cfg, keep = workload.make_batch(config, n)
     ctx.upload_batch(kind, pairs, opt)
