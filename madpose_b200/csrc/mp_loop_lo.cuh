@@ -10,6 +10,7 @@ namespace mp {
 #define MP_CLK_END(C_, slot_) do { if (threadIdx.x == 0) (C_).S->clk[slot_] += (unsigned long long)(clock64() - clk_t0_); } while (0)
 
 constexpr int SH_MAXHEAD = 1024, SH_TAB = 2048;
+constexpr int RS_CH = 8, RS_LD = 33; // warp reduction of the LM sums through shared memory: values per pass, padded row
 
 struct BlockScratch { // shared memory of the decide kernel
     double red[32];
@@ -23,9 +24,13 @@ struct BlockScratch { // shared memory of the decide kernel
     int lm_go;
     LmSetup lm_setup;
     LmDriver drv;
-    // fast Fisher-Yates head: draws, prefetched values, displaced-position hash table
-    int sh_j[SH_MAXHEAD], sh_vi[SH_MAXHEAD], sh_vj[SH_MAXHEAD];
-    int sh_key[SH_TAB], sh_val[SH_TAB];
+    union { // two phases that never overlap share this memory
+        struct { // fast Fisher-Yates head: draws, prefetched values, bucket offsets / entries, predecessor tables
+            int sh_j[SH_MAXHEAD], sh_vi[SH_MAXHEAD], sh_vj[SH_MAXHEAD];
+            int sh_key[SH_TAB], sh_val[SH_TAB];
+        } f;
+        double rs_tile[LP_WIDE_THREADS / 32][RS_CH * RS_LD]; // per warp: the LM evaluation's sums, RS_CH values x 32 lanes at a time
+    } u;
 };
 
 struct BlockCtx {
@@ -72,25 +77,30 @@ template <int KIND> struct BlockEval {
         }
         if (threadIdx.x == 0) C->S->lm_blocks += ntot;
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-        // warp reduce-scatter of the 78 sums (padded to 80): every step halves the number of values a lane carries
-        // (80 -> 40 -> 20 -> 10 -> 5) and the partner distance; 80 shuffled doubles instead of 78 x 5 for butterflies
+        // warp sums of the 78 accumulators through shared memory, RS_CH values at a time: every lane stores its RS_CH
+        // values (row = value, column = lane, padded rows), lane (c, q) = (lane % 8, lane / 8) adds the 8 columns of quarter
+        // q of value c in order, two shuffles combine the quarters.  ~35 instructions per pass, 10 passes; the register
+        // reduce-scatter this replaces (80 -> 40 -> 20 -> 10 -> 5 values per lane with selects around 160 64-bit shuffles)
+        // compiled to 2 200 instructions -- a quarter of the evaluation's instruction stream for ~2 000 residual blocks.
+        // The order of the additions is fixed and does not depend on the CTA width.
         {
             const double *av = reinterpret_cast<const double *>(&a);
-            double v[80];
+            double *tile = sh->u.rs_tile[warp];
+            const int c = lane & (RS_CH - 1), q = lane >> 3;
 #pragma unroll
-            for (int i = 0; i < 80; i++) v[i] = i < LM_ACC_DOUBLES ? av[i] : 0.0;
-#define MP_RS_STEP(H_, BIT_) \
-            { const bool up = (lane & BIT_) != 0; \
-              _Pragma("unroll") for (int i = 0; i < H_; i++) { \
-                  const double keep = up ? v[H_ + i] : v[i], send = up ? v[i] : v[H_ + i]; \
-                  v[i] = keep + __shfl_xor_sync(0xffffffffu, send, BIT_); } }
-            MP_RS_STEP(40, 16) MP_RS_STEP(20, 8) MP_RS_STEP(10, 4) MP_RS_STEP(5, 2)
-#undef MP_RS_STEP
-            const int g0 = ((lane >> 4) & 1) * 40 + ((lane >> 3) & 1) * 20 + ((lane >> 2) & 1) * 10 + ((lane >> 1) & 1) * 5;
+            for (int ch = 0; ch < (LM_ACC_DOUBLES + RS_CH - 1) / RS_CH; ch++) {
 #pragma unroll
-            for (int i = 0; i < 5; i++) {
-                const double s = v[i] + __shfl_xor_sync(0xffffffffu, v[i], 1);
-                if ((lane & 1) == 0 && g0 + i < LM_ACC_DOUBLES) sh->part[warp][g0 + i] = s;
+                for (int k = 0; k < RS_CH; k++)
+                    if (ch * RS_CH + k < LM_ACC_DOUBLES) tile[k * RS_LD + lane] = av[ch * RS_CH + k];
+                __syncwarp();
+                const double *col = tile + c * RS_LD + 8 * q;
+                double s = col[0];
+#pragma unroll
+                for (int k = 1; k < 8; k++) s += col[k];
+                s += __shfl_xor_sync(0xffffffffu, s, 8);
+                s += __shfl_xor_sync(0xffffffffu, s, 16);
+                if (lane < RS_CH && ch * RS_CH + lane < LM_ACC_DOUBLES) sh->part[warp][ch * RS_CH + lane] = s;
+                __syncwarp();
             }
         }
         __syncthreads();
@@ -214,14 +224,14 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
             for (int j = threadIdx.x; j < first && i + j < head; j += blockDim.x) {
                 const uint32_t w = mt_temper(ring_at(j));
                 const int ii = i + j, jj = ii + (int)(((unsigned long long)w * (uint32_t)(n - ii)) >> 32);
-                sh->sh_j[ii] = jj; sh->sh_vi[ii] = v[ii]; sh->sh_vj[ii] = v[jj];
+                sh->u.f.sh_j[ii] = jj; sh->u.f.sh_vi[ii] = v[ii]; sh->u.f.sh_vj[ii] = v[jj];
             }
         __syncthreads();
         if (threadIdx.x == 0) {
             g->pos = pos + first;
             if (first < m) { // the draw with a rejection, sequentially
                 const int ii = i + first, jj = mt_uniform_int(g, ii, n - 1);
-                if (fast && ii < head) { sh->sh_j[ii] = jj; sh->sh_vi[ii] = v[ii]; sh->sh_vj[ii] = v[jj]; }
+                if (fast && ii < head) { sh->u.f.sh_j[ii] = jj; sh->u.f.sh_vi[ii] = v[ii]; sh->u.f.sh_vj[ii] = v[jj]; }
             }
         }
         i += first + (first < m ? 1 : 0);
@@ -237,11 +247,11 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
         // does not matter, a bucket holds ~head / 1024 <= 1 swaps on average) and each query scans one bucket for the
         // maximum -- 8 barriers instead of the 55 stages of a bitonic sort of the (target, time) keys.
         constexpr int NB = 1024;
-        int *start = sh->sh_key, *ent = sh->sh_key + NB;           // bucket offsets (exclusive scan), swap times by bucket
-        int *ps = sh->sh_val, *pt = sh->sh_val + SH_MAXHEAD;       // pt doubles as the scatter cursors first
+        int *start = sh->u.f.sh_key, *ent = sh->u.f.sh_key + NB;           // bucket offsets (exclusive scan), swap times by bucket
+        int *ps = sh->u.f.sh_val, *pt = sh->u.f.sh_val + SH_MAXHEAD;       // pt doubles as the scatter cursors first
         for (int b = threadIdx.x; b < NB; b += blockDim.x) start[b] = 0;
         __syncthreads();
-        for (int k = threadIdx.x; k < head; k += blockDim.x) atomicAdd(&start[sh->sh_j[k] & (NB - 1)], 1);
+        for (int k = threadIdx.x; k < head; k += blockDim.x) atomicAdd(&start[sh->u.f.sh_j[k] & (NB - 1)], 1);
         __syncthreads();
         { // exclusive scan of the 1024 counts: a contiguous run per thread, warp scan, warp totals through sh->wcnt
             const int per = NB / (int)blockDim.x, b0 = threadIdx.x * per; // blockDim is 32, 64 or 128
@@ -257,27 +267,27 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
             for (int q = 0; q < per; q++) { const int c = start[b0 + q]; start[b0 + q] = base; pt[b0 + q] = base; base += c; }
         }
         __syncthreads();
-        for (int k = threadIdx.x; k < head; k += blockDim.x) ent[atomicAdd(&pt[sh->sh_j[k] & (NB - 1)], 1)] = k;
+        for (int k = threadIdx.x; k < head; k += blockDim.x) ent[atomicAdd(&pt[sh->u.f.sh_j[k] & (NB - 1)], 1)] = k;
         __syncthreads();
         auto latest_before = [&](int target, int before) { // max i < before with j_i == target, or -1
             const int b = target & (NB - 1), e1 = b + 1 < NB ? start[b + 1] : head;
             int best = -1;
-            for (int e = start[b]; e < e1; e++) { const int i = ent[e]; if (i < before && i > best && sh->sh_j[i] == target) best = i; }
+            for (int e = start[b]; e < e1; e++) { const int i = ent[e]; if (i < before && i > best && sh->u.f.sh_j[i] == target) best = i; }
             return best;
         };
         // (the cursors in pt are dead after the barrier above; the queries read start / ent / sh_j only)
-        for (int k = threadIdx.x; k < head; k += blockDim.x) { ps[k] = latest_before(sh->sh_j[k], k); pt[k] = latest_before(k, k); }
+        for (int k = threadIdx.x; k < head; k += blockDim.x) { ps[k] = latest_before(sh->u.f.sh_j[k], k); pt[k] = latest_before(k, k); }
         const int last_hit = (head == n - 1 && n - 1 < target) ? latest_before(n - 1, head) : -1; // (every swap time is < head)
         __syncthreads();
         auto a_of = [&](int c) {
             while (pt[c] >= 0) c = pt[c];
-            return sh->sh_vi[c];
+            return sh->u.f.sh_vi[c];
         };
         for (int k = threadIdx.x; k < head; k += blockDim.x) {
-            const int j = sh->sh_j[k];
+            const int j = sh->u.f.sh_j[k];
             int out;
             if (j == k) out = a_of(k);
-            else { const int q = ps[k]; out = q >= 0 ? a_of(q) : sh->sh_vj[k]; }
+            else { const int q = ps[k]; out = q >= 0 ? a_of(q) : sh->u.f.sh_vj[k]; }
             v[k] = out;
         }
         if (threadIdx.x == 0 && last_hit >= 0) v[n - 1] = a_of(last_hit); // the list grows: its last element is kept too
