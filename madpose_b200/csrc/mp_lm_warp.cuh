@@ -12,6 +12,10 @@
 namespace mp {
 
 constexpr unsigned LMW_FULL = 0xffffffffu;
+// The driver state, its set-up and the evaluation's totals live in the CTA's shared memory (BlockScratch): telling the
+// compiler turns the generic loads / stores of these out-of-line functions (each with its descriptor moves: a fifth of
+// their instructions) into plain shared-memory accesses.
+#define LMW_SHARED(p_) __builtin_assume(__isShared(p_))
 constexpr int LM_TRI = LM_NT * (LM_NT + 1) / 2;
 
 // reduced full-slot sums (LmAcc as a flat array) -> compact nt x nt system; = lm_compress.  The map from the 66 upper-
@@ -87,7 +91,9 @@ __device__ __forceinline__ double warp_grad_max(const LmSetup &L, const double *
 #define LMW_T(slot_) do { } while (0)
 #endif
 static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot, int lane) {
+    LMW_SHARED(&d); LMW_SHARED(tot);
     const LmSetup &L = *d.L;
+    LMW_SHARED(&L);
     LMW_T0();
     const int nt = L.nt;
     warp_compress_table(d, lane);
@@ -125,7 +131,9 @@ static __device__ __noinline__ bool warp_lm_first(LmDriver &d, const double *tot
 // shuffle + read-modify-write loop of up to 10 trips per step).  The arithmetic -- operands, order of the sums, fused
 // multiply-adds -- is the row form's.
 static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
+    LMW_SHARED(&d);
     const LmSetup &L = *d.L;
+    LMW_SHARED(&L);
     const int nt = L.nt;
     constexpr int S = LM_NT;
     double *M = d.Lc, *Lf = d.As;
@@ -265,7 +273,9 @@ static __device__ __noinline__ bool warp_lm_propose(LmDriver &d, int lane) {
 
 // LmDriver::feed
 static __device__ __noinline__ bool warp_lm_feed(LmDriver &d, const double *tot, int lane) {
+    LMW_SHARED(&d); LMW_SHARED(tot);
     const LmSetup &L = *d.L;
+    LMW_SHARED(&L);
     LMW_T0();
     int verdict = 0; // 0 finished, 1 rejected step (continue), 2 accepted step
     double cc = 0, rel = 0;

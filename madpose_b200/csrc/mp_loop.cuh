@@ -126,6 +126,7 @@ struct LoopBuffers {
 // exact ScoreModel (hybrid_ransac.h:265-282) of one model by the whole CTA
 static __device__ __noinline__ double block_score64(const PairConst &pc, const Match64 *m, const Model &model,
                                                 int score_type, double *red) {
+    __builtin_assume(__isGlobal(&pc)); __builtin_assume(__isGlobal(m)); __builtin_assume(__isShared(red)); // address-space hints (mp_lm_warp.cuh)
     Eval64 e;
     make_eval64(pc, model, &e);
     double acc = 0;
@@ -152,6 +153,8 @@ struct InlScratch { int cnt[3][INL_CH * INL_MAXW]; int base[3]; };
 static __device__ __noinline__ void block_inliers(const PairConst &pc, const Match64 *m, const Model &model,
                                            const double *thr3, int *out_idx, int *cnt_sh, int (*wcnt)[16],
                                            double *score_out = nullptr, int score_type = 0, double *red = nullptr) {
+    __builtin_assume(__isGlobal(&pc)); __builtin_assume(__isGlobal(m)); __builtin_assume(__isGlobal(out_idx));
+    __builtin_assume(__isShared(cnt_sh)); __builtin_assume(__isShared(wcnt)); // address-space hints (mp_lm_warp.cuh)
     __shared__ InlScratch isc;
     Eval64 e;
     make_eval64(pc, model, &e);

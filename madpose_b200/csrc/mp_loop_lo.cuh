@@ -63,6 +63,7 @@ template <int KIND> struct BlockEval {
     __device__ __noinline__ void operator()() const {
         MP_CLK_BEGIN();
         BlockScratch *sh = C->sh;
+        __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(L)); // (address-space hints: see mp_lm_warp.cuh)
         LmPoint p;
         lm_point(KIND, sh->lm_x, &p);
         LmAcc a;
@@ -121,6 +122,7 @@ template <int KIND> __device__ __noinline__ void block_lm(const BlockCtx &C, con
                                              const Model &start, Model *out, LmInfo *info_out) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
+    __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(&L)); __builtin_assume(__isShared(&start)); __builtin_assume(__isShared(out));
     LmDriver &drv = sh->drv; // driven by thread 0 only; shared memory keeps its arrays off the local-memory path
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -189,6 +191,7 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
     MP_CLK_BEGIN();
     MtStream *g = C.rngB;
     BlockScratch *sh = C.sh;
+    __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(len_sh)); __builtin_assume(__isGlobal(g)); __builtin_assume(__isGlobal(v));
     __syncthreads();
     const int n = *len_sh;
     __syncthreads();
@@ -306,6 +309,7 @@ static __device__ __noinline__ void block_shuffle_resize(const BlockCtx &C, int 
 static __device__ __noinline__ void block_unflatten(const BlockCtx &C, const int *flat, int len, int *cnt3_sh) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
+    __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(cnt3_sh)); __builtin_assume(__isGlobal(flat)); __builtin_assume(__isGlobal(C.sample));
     const int n = C.pc->n;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     __syncthreads();
@@ -345,6 +349,8 @@ static __device__ __noinline__ void block_unflatten(const BlockCtx &C, const int
 template <int KIND> __device__ __noinline__ void block_lsq_fit(const BlockCtx &C, const double *thr, int solver, Model *m,
                                                   bool all_inliers, bool have_inliers = false) {
     BlockScratch *sh = C.sh;
+    __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(m)); __builtin_assume(__isShared(C.S));
+    __builtin_assume(__isGlobal(C.inl_cur)); __builtin_assume(__isGlobal(C.flat)); __builtin_assume(__isGlobal(C.pc));
     const int n = C.pc->n;
     if (!have_inliers) { MP_CLK_BEGIN(); block_inliers(*C.pc, C.M, *m, thr, C.inl_cur, sh->cnt, sh->wcnt); MP_CLK_END(C, 1); }
     if (threadIdx.x == 0) { C.S->evals64 += n; trace_event(C, -2.0, (double)sh->cnt[0] + 131072.0 * (double)sh->cnt[1] + 17179869184.0 * (double)sh->cnt[2]); }
@@ -395,6 +401,8 @@ template <int KIND> __device__ __noinline__ void block_local_optimization(const 
                                                              double *best_score, int *best_solver) {
     MP_CLK_BEGIN();
     BlockScratch *sh = C.sh;
+    __builtin_assume(__isShared(sh)); __builtin_assume(__isShared(best)); __builtin_assume(__isShared(best_score)); __builtin_assume(__isShared(best_solver));
+    __builtin_assume(__isShared(C.S)); __builtin_assume(__isGlobal(C.inl_cur)); __builtin_assume(__isGlobal(C.base)); __builtin_assume(__isGlobal(C.pc));
     const PairConst &pc = *C.pc;
     const mp_options &o = C.prm->opt;
     const int n = pc.n;
