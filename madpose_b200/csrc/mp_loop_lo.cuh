@@ -364,9 +364,13 @@ template <int KIND> __device__ __noinline__ void block_lsq_fit(const BlockCtx &C
     const int mult = C.prm->opt.min_sample_multiplicator;
     const int k0 = min(sz[0] * mult, c0), k1 = min(sz[1] * mult, c1), k2 = min(sz[2] * mult, c2);
     const int total = (k0 + k1 + k2) * mult; // x7 applied twice (quirk Q4)
-    for (int k = threadIdx.x; k < c0; k += blockDim.x) C.flat[k] = C.inl_cur[k];
-    for (int k = threadIdx.x; k < c1; k += blockDim.x) C.flat[c0 + k] = C.inl_cur[n + k] + n;
-    for (int k = threadIdx.x; k < c2; k += blockDim.x) C.flat[c0 + c1 + k] = C.inl_cur[2 * n + k] + 2 * n;
+    {
+        int *flat = C.flat; const int *cur = C.inl_cur; // (local copies carry the address-space hints)
+        __builtin_assume(__isGlobal(flat)); __builtin_assume(__isGlobal(cur));
+        for (int k = threadIdx.x; k < c0; k += blockDim.x) flat[k] = cur[k];
+        for (int k = threadIdx.x; k < c1; k += blockDim.x) flat[c0 + k] = cur[n + k] + n;
+        for (int k = threadIdx.x; k < c2; k += blockDim.x) flat[c0 + c1 + k] = cur[2 * n + k] + 2 * n;
+    }
     __syncthreads();
     if (threadIdx.x == 0) sh->fit_len = c0 + c1 + c2;
     block_shuffle_resize(C, total, C.flat, &sh->fit_len);
@@ -425,9 +429,13 @@ template <int KIND> __device__ __noinline__ void block_local_optimization(const 
     update_best(sc, &sh->m_init);
     if (threadIdx.x == 0) { C.S->evals64 += n; trace_event(C, -2.0, (double)sh->cnt[0] + 131072.0 * (double)sh->cnt[1] + 17179869184.0 * (double)sh->cnt[2]); }
     const int c0 = sh->cnt[0], c1 = sh->cnt[1], c2 = sh->cnt[2];
-    for (int k = threadIdx.x; k < c0; k += blockDim.x) C.base[k] = C.inl_cur[k];
-    for (int k = threadIdx.x; k < c1; k += blockDim.x) C.base[c0 + k] = C.inl_cur[n + k] + n;
-    for (int k = threadIdx.x; k < c2; k += blockDim.x) C.base[c0 + c1 + k] = C.inl_cur[2 * n + k] + 2 * n;
+    {
+        int *base = C.base; const int *cur = C.inl_cur;
+        __builtin_assume(__isGlobal(base)); __builtin_assume(__isGlobal(cur));
+        for (int k = threadIdx.x; k < c0; k += blockDim.x) base[k] = cur[k];
+        for (int k = threadIdx.x; k < c1; k += blockDim.x) base[c0 + k] = cur[n + k] + n;
+        for (int k = threadIdx.x; k < c2; k += blockDim.x) base[c0 + c1 + k] = cur[2 * n + k] + 2 * n;
+    }
     __syncthreads();
     if (threadIdx.x == 0) sh->base_len = c0 + c1 + c2; // current length of the base list
     __syncthreads();
