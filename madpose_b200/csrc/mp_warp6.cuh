@@ -282,19 +282,22 @@ __device__ inline int group_motion_from_essential(const Warp6Work &W, const doub
 // LOCKSTEP: all warps of the CTA call it together (valid = this warp has a sample) and meet at a CTA barrier between
 // the stages, so that they execute the same stage's code at the same time (the solver is ~170 KB of instructions).
 template <bool LOCKSTEP> __device__ inline int warp_relpose_6pt(Warp6Work &W, Model *out, int lane, bool valid = true) {
+#ifndef W6_BARRIERS
+#define W6_BARRIERS 15 // which of the four stage barriers the lockstep form keeps (bit k = the barrier after stage k)
+#endif
     if (valid) warp6_nullspace(W, lane);
-    if (LOCKSTEP) __syncthreads();
+    if (LOCKSTEP && (W6_BARRIERS & 1)) __syncthreads();
     bool ok = valid;
     if (ok) ok = warp6_build(W, lane);
-    if (LOCKSTEP) __syncthreads();
+    if (LOCKSTEP && (W6_BARRIERS & 2)) __syncthreads();
     if (ok) warp6_dets(W, lane);
-    if (LOCKSTEP) __syncthreads();
+    if (LOCKSTEP && (W6_BARRIERS & 4)) __syncthreads();
     int nr = 0;
     if (ok) {
         warp6_coefs(W, lane);
         nr = warp_real_roots<15>(W.coef, 15, W.roots, W.u.poly, true, lane);
     }
-    if (LOCKSTEP) __syncthreads();
+    if (LOCKSTEP && (W6_BARRIERS & 8)) __syncthreads();
     __syncwarp();
     int n = 0;
     const int g = lane / 10, r = lane % 10;
