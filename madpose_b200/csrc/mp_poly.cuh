@@ -49,6 +49,10 @@ template <int MAXD> struct Sturm {
 
     // p has exact degree n >= 2 (leading coefficient non-negligible)
     MP_HD void build(const double *p, int n) {
+#pragma unroll
+        for (int k = 0; k <= MAXD; k++) // rows stay zero above their degree: changes() evaluates them at full length
+#pragma unroll
+            for (int i = 0; i <= MAXD; i++) c[k][i] = 0.0;
         for (int i = 0; i <= n; i++) c[0][i] = p[i];
         deg[0] = n;
         for (int i = 1; i <= n; i++) c[1][i - 1] = i * p[i];
@@ -69,14 +73,28 @@ template <int MAXD> struct Sturm {
             for (int i = 0; i <= nr; i++) { r[i] = -r[i]; mx = fmax(mx, fabs(r[i])); }
             if (!(mx > 0.0)) break;
             while (nr > 0 && fabs(r[nr]) <= 1e-13 * mx) nr--;
+            for (int i = nr + 1; i <= MAXD; i++) r[i] = 0.0; // (what the division left above the degree, and trimmed terms)
             deg[len] = nr;
             len++;
         }
     }
+    // Every chain polynomial is evaluated at the full length MAXD with its zero padding (fma(0, x, c) == c: the values are
+    // those of the exact-degree Horner form): fixed trip counts and static offsets let the rows' chains run side by side
+    // instead of one data-dependent loop after the other.
     MP_HD int changes(double x) const {
+        double vals[MAXD + 1];
+#pragma unroll
+        for (int k = 0; k <= MAXD; k++) {
+            double r = c[k][MAXD];
+#pragma unroll
+            for (int i = MAXD - 1; i >= 0; i--) r = fma(r, x, c[k][i]);
+            vals[k] = r;
+        }
         int n = 0, last = 0;
-        for (int k = 0; k < len; k++) {
-            double v = poly_val(c[k], deg[k], x);
+#pragma unroll
+        for (int k = 0; k <= MAXD; k++) {
+            if (k >= len) break;
+            const double v = vals[k];
             int s = (v > 0) - (v < 0);
             if (s != 0) {
                 if (last != 0 && s != last) n++;
